@@ -1,0 +1,187 @@
+/*
+ * b200attn.h -- C ABI of the B200 (sm_100a) paged-KV attention library.
+ *
+ * This is the drop-in boundary of the project: a plain `extern "C"` surface (raw
+ * device pointers, sizes, strides, a cudaStream_t) with no torch types.  The
+ * Python `B200AttnBackend` (sglang_custom_b200/backend.py) binds it with ctypes;
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Every entry point below replaces one piece of the reference's attention hot
+ * path (paths relative to the reference root, python/sglang/srt/...):
+ *
+ *   b200attn_kv_write            mem_cache/memory_pool.py:420-458  MHATokenToKVPool.set_kv_buffer
+ *   b200attn_decode_plan         layers/attention/triton_backend.py:160-226,875-924 (init_forward_metadata,
+ *                                get_num_kv_splits_triton) -- device-only, CUDA-graph safe
+ *   b200attn_decode              layers/attention/torch_native_backend.py:112-180,226-267 (oracle),
+ *                                triton_ops/decode_attention.py:677-728, sgl-kernel/csrc/cpu/decode.cpp:1375
+ *   b200attn_decode (merge part) triton_ops/decode_attention.py:492-552, decode.cpp:812-860
+ *   b200attn_merge_state         layers/attention/merge_state.py:26-46,
+ *                                sgl-kernel/csrc/attention/merge_attn_states.cu:32-106
+ *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
+ *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
+ *   b200attn_flatten_kv_indices  layers/attention/utils.py:5-41 (create_flashinfer_kv_indices_triton)
+ *   b200attn_gather_kv           torch_native_backend.py:92-94,155-157 (k_cache[per_req_tokens] page gather)
+ *
+ * Conventions
+ *   - All pointers are DEVICE pointers unless the name ends in `_host`.
+ *   - The library never allocates or frees device memory and never synchronises
+ *     the host with the device; every kernel is enqueued on `stream`.
+ *     All calls are CUDA-graph-capture safe.
+ *   - Return value: 0 on success, a negative B200ATTN_ERR_* code otherwise; the
+ *     message is available (per thread) from b200attn_last_error().
+ *   - Strides are in ELEMENTS of the tensor's own dtype unless stated.
+ *   - Index tensors `req_pool_indices`/`seq_lens` may be int32 (CUDA-graph
+ *     buffers, cuda_graph_runner.py:273-276) or int64 (eager,
+ *     schedule_batch.py:1125-1133): `idx_is_i64` says which.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_VERSION 100 /* 0.1.0 */
+
+/* element types */
+#define B200ATTN_BF16 0
+#define B200ATTN_F16 1
+#define B200ATTN_FP8_E4M3 2 /* torch.float8_e4m3fn, stored as uint8 in the pool */
+#define B200ATTN_F32 3
+
+/* error codes */
+#define B200ATTN_OK 0
+#define B200ATTN_ERR_INVALID (-1)     /* bad argument (shape, alignment, null) */
+#define B200ATTN_ERR_UNSUPPORTED (-2) /* valid in the reference, not built here */
+#define B200ATTN_ERR_CUDA (-3)        /* a CUDA runtime call failed */
+#define B200ATTN_ERR_WORKSPACE (-4)   /* workspace / plan buffer too small */
+
+/* how the FP8 scale is applied before the e4m3 cast (both are torch behaviours):
+ *   DIV: bf16(x / s)      -- torch CPU `div_`, and CUDA `div_` by a 0-dim tensor
+ *   RCP: bf16(x * (1/s))  -- torch CUDA `div_` by a python float (BinaryDivTrueKernel.cu) */
+#define B200ATTN_SCALE_DIV 0
+#define B200ATTN_SCALE_RCP 1
+
+typedef void* b200attn_stream_t; /* cudaStream_t */
+
+int b200attn_version(void);
+const char* b200attn_last_error(void);
+
+/* Device facts the host side needs for sizing (no allocation). */
+int b200attn_device_info(int* sm_count, int* cc_major, int* cc_minor, int* max_smem_optin);
+
+/* ---------------------------------------------------------------- KV write
+ * pool[loc[t], h, :] = cast(k[t, h, :])  for t in [0,T), h in [0,Hkv)   (same for v)
+ * Replaces MHATokenToKVPool.set_kv_buffer (memory_pool.py:420-458).
+ *   k, v            [T, Hkv, D] in_dtype (bf16/f16); token stride k_tok_stride, head stride k_head_stride
+ *   loc             [T] int64, values in [0, P)
+ *   k_pool, v_pool  [P, Hkv, D] pool_dtype; token stride pool_tok_stride (elements), head stride D
+ *   pool_dtype == in_dtype      : bit copy
+ *   pool_dtype == FP8_E4M3      : x -> bf16(x / scale) -> e4m3 (RNE, torch overflow rule)
+ *   k_scale/v_scale: if *_scale_dev != NULL it points at n_scales (1 or Hkv) fp32
+ *   values on the device (a 0-dim Parameter, or a per-head vector); otherwise the
+ *   host scalar *_scale_host is used; a host scalar of 0 means "no scaling" (None).
+ *   writeback_scaled != 0 reproduces the reference's in-place `cache_k.div_(scale)`
+ *   side effect on the caller's k/v tensors (memory_pool.py:437-440).
+ * Duplicate `loc` entries (padded CUDA-graph rows all map to slot 0) are
+ * last-writer-wins in the reference; here the order is unspecified, which only
+ * matters for the dummy slot. */
+int b200attn_kv_write(const void* k, const void* v, int64_t k_tok_stride, int64_t k_head_stride,
+                      int64_t v_tok_stride, int64_t v_head_stride, const int64_t* loc, int T, int Hkv,
+                      int D, void* k_pool, void* v_pool, int64_t pool_tok_stride, int in_dtype,
+                      int pool_dtype, float k_scale_host, float v_scale_host, const float* k_scale_dev,
+                      const float* v_scale_dev, int n_scales, int scale_mode, int writeback_scaled,
+                      b200attn_stream_t stream);
+
+/* ---------------------------------------------------------------- decode
+ * Split-KV plan, computed on the device from seq_lens (no host sync, graph safe).
+ *
+ * The decode kernel is persistent: n_ctas CTAs (a multiple of the SM count).  Every
+ * request's KV range is measured in 16-token units; the flattened unit space of the
+ * whole batch is cut into n_ctas equal shares of W = max(min_units_per_cta,
+ * ceil(total_units / n_ctas)) units, so ragged batches stay balanced.  A request
+ * that falls entirely inside one share is finished by that CTA; a request cut
+ * across shares produces one fp32 partial per share, combined by the LSE merge.
+ *
+ * plan layout (int32): [0] total_units [1] W [2] bs [3] n_ctas [4..7] reserved,
+ *   then cum[bs+1] (exclusive prefix sum of units), then first_req[n_ctas].
+ */
+size_t b200attn_decode_plan_bytes(int max_bs, int n_ctas);
+int b200attn_decode_plan(const void* seq_lens, int idx_is_i64, int bs, int n_ctas,
+                         int min_units_per_cta, int32_t* plan, size_t plan_bytes,
+                         b200attn_stream_t stream);
+
+/* fp32 workspace for split partials: 2 * n_ctas * Hq * (Dv + 1) floats */
+size_t b200attn_decode_workspace_bytes(int n_ctas, int Hq, int Dv);
+
+/* Paged decode attention (one query token per request) + LSE merge of the splits.
+ *   q        [bs, Hq, D] bf16/f16, token stride q_tok_stride (head stride D)
+ *   out      [bs, Hq, D] same dtype as q, token stride out_tok_stride
+ *   k_pool, v_pool [P, Hkv, D] kv_dtype (bf16/f16 == q dtype, or FP8_E4M3), token stride pool_tok_stride
+ *   req_to_token   [max_reqs, table_stride] int32 : token slot of (request row, position)
+ *   req_pool_indices [bs], seq_lens [bs]  (int32 or int64)
+ *   out[i,h] = softmax(sm_scale * k_scale * q[i,h] . K[idx_i, h/G]^T) . V[idx_i, h/G] * v_scale,
+ *   idx_i = req_to_token[req_pool_indices[i], 0:seq_lens[i]]   (torch_native_backend.py:147-177)
+ *   logit_cap > 0 applies cap*tanh(x/cap) to the scaled logits (decode_attention.py:117-118).
+ *   plan must have been produced by b200attn_decode_plan for the same seq_lens, bs and n_ctas.
+ *   If lse_out != NULL, the natural-log LSE of every (request, head) is stored there (fp32 [bs,Hq]). */
+int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                    const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                    const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                    const void* seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype,
+                    int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
+                    const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
+                    float* lse_out, b200attn_stream_t stream);
+
+/* ---------------------------------------------------------------- 2-way LSE merge
+ * out = (e^{la-m} a + e^{lb-m} b) / (e^{la-m} + e^{lb-m}),  lse = log(sum) + m, m = max(la, lb);
+ * +inf LSE is treated as -inf (merge_attn_states.cu:47-50).
+ *   a, b, out [T, H, D] dtype (bf16/f16/f32), contiguous; lse_* [T, H] fp32; out_lse may be NULL */
+int b200attn_merge_state(const void* a, const float* lse_a, const void* b, const float* lse_b,
+                         void* out, float* out_lse, int T, int H, int D, int dtype,
+                         b200attn_stream_t stream);
+
+/* ---------------------------------------------------------------- extend / prefill
+ * Causal attention of E_i new query tokens per request over P_i cached prefix
+ * tokens plus the E_i new tokens, all read from the paged pool through
+ * req_to_token (the new tokens must already be written: b200attn_kv_write first,
+ * exactly as torch_native_backend.py:196-199 does).
+ *   q   [T, Hq, D], out [T, Hq, D]  (T = sum E_i), token strides given
+ *   extend_seq_lens [bs] int32 (E_i), extend_prefix_lens [bs] int32 (P_i),
+ *   extend_start_loc [bs] int32 (row of request i's first query in q/out)
+ *   seq_lens[i] must equal P_i + E_i.
+ *   key j of request i is visible to its query t iff j <= P_i + t (causal != 0), else all keys.
+ *   max_extend_len: upper bound of E_i known on the host (grid sizing, no device sync). */
+int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                    const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                    const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                    const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
+                    const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
+                    int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                    float logit_cap, float k_scale, float v_scale, int causal, int impl,
+                    b200attn_stream_t stream);
+#define B200ATTN_EXTEND_AUTO 0
+#define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */
+#define B200ATTN_EXTEND_MMA 2     /* register-MMA kernel (short / ragged rows, FP8 KV, D == 64) */
+
+/* ---------------------------------------------------------------- page-table utilities
+ * kv_indices[kv_indptr[i] + j] = req_to_token[req_pool_indices[i], kv_start[i] + j], j < lens[i]
+ * (layers/attention/utils.py:5-41).  kv_start may be NULL (0). lens/kv_start/req_pool_indices share idx_is_i64;
+ * kv_indptr is int32. */
+int b200attn_flatten_kv_indices(const int32_t* req_to_token, int64_t table_stride,
+                                const void* req_pool_indices, const void* lens, const void* kv_start,
+                                int idx_is_i64, const int32_t* kv_indptr, int32_t* kv_indices, int bs,
+                                b200attn_stream_t stream);
+
+/* dst[j, :, :] = pool[indices[j], :, :]  -- the page gather `k_cache[per_req_tokens]`, bit exact.
+ *   row_bytes = Hkv * D * sizeof(elem) (multiple of 16), pool_tok_stride_bytes likewise */
+int b200attn_gather_kv(const void* pool, int64_t pool_tok_stride_bytes, const int32_t* indices,
+                       int64_t n, int64_t row_bytes, void* dst, b200attn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,671 @@
+// Paged split-KV decode attention for sm_100a.
+//
+// Reference semantics: python/sglang/srt/layers/attention/torch_native_backend.py:112-180
+// (per request: gather K/V rows through req_to_token, softmax(q K^T * scale) V, no causal mask);
+// GPU designs it supersedes: triton_ops/decode_attention.py:45-552 (stage1 + stage2) and the
+// sgl-kernel CPU flash-decoding sgl-kernel/csrc/cpu/decode.cpp:863-1373.
+//
+// Design (HBM-bound: the job is to keep >= 64 KiB of row gathers in flight per SM)
+//   * persistent grid: n_ctas CTAs (one or two per SM); the device-side plan
+//     (decode_plan.cu) hands every CTA an equal share of the flattened
+//     16-token units of the batch, so ragged batches stay balanced without a host sync.
+//   * a CTA owns HB kv heads (HB = 8 for Llama-3-8B: the K row of one token for
+//     all 8 heads is one contiguous 2 KiB segment of the pool) and walks its
+//     share in tiles of NT tokens; rows are gathered straight from the pool through
+//     req_to_token with 16-byte cp.async (LDGSTS) into a 3-stage XOR-swizzled
+//     shared-memory ring -- no flattened kv_indices copy is ever built.
+//   * warp (hb, ts) computes 16 tokens of head hb per tile: the GQA group is
+//     packed as the M dimension of mma.sync.m16n8k16 (S = Q K^T, O += P V),
+//     fp32 online softmax with quad shuffles; FP8-E4M3 K/V are dequantised in
+//     registers (cvt.rn.f16x2.e4m3x2) on their way into the MMA.
+//   * a request handled entirely by one CTA is normalised and written directly;
+//     otherwise the CTA writes a normalised fp32 partial + LSE and the merge
+//     kernel (below) combines the pieces.
+#include "common.cuh"
+#include "decode_plan.cuh"
+
+namespace b200attn {
+
+struct DecodeParams {
+  const void* q;
+  void* out;
+  const void* k_pool;
+  const void* v_pool;
+  const int32_t* req_to_token;
+  const void* req_pool_indices;
+  const void* seq_lens;
+  const int32_t* plan;
+  float* ws_o;    // [2*n_ctas*HG][Hq... see slot layout
+  float* ws_lse;
+  float* lse_out;
+  int64_t q_tok_stride, out_tok_stride, pool_tok_stride, table_stride;
+  int idx_is_i64;
+  int bs, Hq, Hkv, G;
+  int n_ctas;
+  float scale_log2;  // sm_scale * k_scale * log2(e)   (logit_cap == 0)
+  float scale_raw;   // sm_scale * k_scale
+  float logit_cap;
+  float v_scale;
+};
+
+constexpr int kDecodeThreads = 256;
+constexpr int kDecodeWarps = 8;
+constexpr int kMaxSeg = 32;
+
+template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE>
+struct DecodeCfg {
+  static constexpr int TS = kDecodeWarps / HB;       // token sub-tiles (warps) per head
+  static constexpr int NT = 16 * TS;                 // tokens per tile
+  static constexpr int HEADB = D * KVB;              // bytes of one head row
+  static constexpr int ROWB = HB * HEADB;            // bytes gathered per token (K or V)
+  static constexpr int CPH = HEADB / 16;             // 16-byte chunks per head row
+  static constexpr int CPR = ROWB / 16;              // chunks per token row
+  static constexpr int TILEB = NT * ROWB;            // bytes of a K (or V) tile
+  static constexpr int STAGEB = 2 * TILEB;
+  static constexpr int CHUNKS = NT * CPR;            // 16-byte chunks per K tile
+  static constexpr int ITERS = CHUNKS / kDecodeThreads;
+  static constexpr int SWZ = CPH >= 8 ? 7 : (CPH - 1);
+  static_assert(CHUNKS % kDecodeThreads == 0, "tile must divide over the CTA");
+  static constexpr int RED_ROWS = 16;
+  // the cross-warp merge buffer aliases the stage that was consumed last (see the tree merge)
+  static constexpr int REDB = (TS > 1) ? (kDecodeWarps / 2) * RED_ROWS * (D + 2) * 4 : 0;
+  static constexpr bool RED_ALIAS = REDB <= STAGEB;  // else a dedicated buffer after the index ring
+  static constexpr int IDXB = (NSTAGE + 1) * NT * 4;
+  static constexpr int SMEM = NSTAGE * STAGEB + IDXB + (RED_ALIAS ? 0 : REDB) + 128;
+};
+
+struct Segment {
+  int batch;      // request position in the batch
+  int tok_begin;  // first kv position of this piece
+  int tok_end;    // one past the last kv position
+  int slot;       // -1: write final output; else workspace slot
+  int64_t table_off;  // req_pool_index * table_stride
+};
+
+// ---------------------------------------------------------------------------------------
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE>
+__global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeParams p) {
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
+  constexpr bool kFp8 = (KVB == 1);
+  constexpr bool kMmaBf16 = kQBf16 && !kFp8;  // fp8 K/V are dequantised to f16 (exact)
+  constexpr int TS = Cfg::TS, NT = Cfg::NT;
+  constexpr int KSTEPS = D / 16;
+  constexpr int NBLK = D / 8;
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* stage_base = smem;
+  int32_t* idx_ring = reinterpret_cast<int32_t*>(smem + NSTAGE * Cfg::STAGEB);
+  __shared__ Segment segs[kMaxSeg];
+  __shared__ int n_segs_sh;
+  __shared__ int next_req_sh, next_unit_sh;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int hb = warp % HB;   // head within the CTA's head block
+  const int ts = warp / HB;   // token sub-tile
+  const int qd = lane & 3;    // quad lane
+  const int row = lane >> 2;  // MMA row 0..7
+  const int cta = blockIdx.x;
+  const int kv_head = blockIdx.y * HB + hb;
+  const int G = p.G;
+
+  const int32_t* plan = p.plan;
+  const int total_units = plan[kPlanTotalUnits];
+  const int W = plan[kPlanUnitsPerCta];
+  const int bs = p.bs;
+  const int32_t* cum = plan + kPlanHeader;               // [bs + 1]
+  const int32_t* first_req = plan + kPlanHeader + bs + 1; // [n_ctas]
+  const int u_begin = cta * W;
+  if (u_begin >= total_units) return;
+  const int u_end = min(u_begin + W, total_units);
+
+  if (tid == 0) {
+    next_req_sh = first_req[cta];
+    next_unit_sh = u_begin;
+  }
+  __syncthreads();
+
+  const uint8_t* kpool = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
+  const uint8_t* vpool = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
+  const int64_t pool_row_bytes = p.pool_tok_stride * KVB;
+
+  while (true) {
+    // ---------------- build the next batch of segments (thread 0), at most kMaxSeg
+    if (tid == 0) {
+      int i = next_req_sh, u = next_unit_sh, n = 0;
+      while (u < u_end && n < kMaxSeg) {
+        while (cum[i + 1] <= u) ++i;
+        const int c0 = cum[i], c1 = cum[i + 1];
+        const int seg_end = min(c1, u_end);
+        const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
+        Segment s;
+        s.batch = i;
+        s.tok_begin = (u - c0) * kUnit;
+        s.tok_end = min((seg_end - c0) * kUnit, L);
+        const bool is_first = (u == c0), is_last = (seg_end == c1);
+        s.slot = (is_first && is_last) ? -1 : (is_first ? 2 * cta + 1 : 2 * cta);
+        s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride;
+        segs[n++] = s;
+        u = seg_end;
+      }
+      n_segs_sh = n;
+      next_req_sh = i;
+      next_unit_sh = u;
+    }
+    __syncthreads();
+    const int n_segs = n_segs_sh;
+    if (n_segs == 0) break;
+
+    // ---------------- producer cursor: walks (segment, tile) pairs of this batch
+    int p_seg = 0, p_tile = 0;  // next tile to issue
+    int p_count = 0;            // tiles issued so far
+    int p_idx_seg = 0, p_idx_tile = 0, p_idx_count = 0;  // next tile whose indices get staged
+
+    auto seg_tiles = [&](int s) { return (segs[s].tok_end - segs[s].tok_begin + NT - 1) / NT; };
+
+    // stage the token slots of one tile into the index ring (first NT threads)
+    auto stage_indices = [&]() {
+      if (p_idx_seg >= n_segs) return;
+      if (tid < NT) {
+        const Segment& s = segs[p_idx_seg];
+        const int tok = s.tok_begin + p_idx_tile * NT + tid;
+        int32_t slot = -1;
+        if (tok < s.tok_end) slot = __ldg(p.req_to_token + s.table_off + tok);
+        idx_ring[(p_idx_count % (NSTAGE + 1)) * NT + tid] = slot;
+      }
+      ++p_idx_count;
+      if (++p_idx_tile >= seg_tiles(p_idx_seg)) { p_idx_tile = 0; ++p_idx_seg; }
+    };
+
+    // issue the gathers of one tile (all threads); always commits a group
+    auto issue_tile = [&]() {
+      if (p_seg < n_segs) {
+        const int32_t* idx = idx_ring + (p_count % (NSTAGE + 1)) * NT;
+        uint8_t* kst = stage_base + (p_count % NSTAGE) * Cfg::STAGEB;
+        const uint32_t k_s = smem_u32(kst), v_s = k_s + Cfg::TILEB;
+#pragma unroll
+        for (int it = 0; it < Cfg::ITERS; ++it) {
+          const int c = it * kDecodeThreads + tid;
+          const int tok = c / Cfg::CPR;
+          const int cr = c % Cfg::CPR;
+          const int head = cr / Cfg::CPH, ch = cr % Cfg::CPH;
+          const int32_t slot = idx[tok];
+          const int valid = slot >= 0 ? 16 : 0;
+          const int64_t src = static_cast<int64_t>(slot >= 0 ? slot : 0) * pool_row_bytes + cr * 16;
+          const uint32_t dst = tok * Cfg::ROWB + head * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4);
+          cp_async16(k_s + dst, kpool + src, valid);
+          cp_async16(v_s + dst, vpool + src, valid);
+        }
+        ++p_count;
+        if (++p_tile >= seg_tiles(p_seg)) { p_tile = 0; ++p_seg; }
+      }
+      cp_async_commit();
+    };
+
+    // prologue: indices for the first NSTAGE tiles, gathers for the first NSTAGE-1
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) stage_indices();
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < NSTAGE - 1; ++s) issue_tile();
+
+    int c_count = 0;  // tiles consumed
+    for (int sg = 0; sg < n_segs; ++sg) {
+      const Segment seg = segs[sg];
+      const int ntiles = (seg.tok_end - seg.tok_begin + NT - 1) / NT;
+
+      // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
+      uint32_t qa[KSTEPS][4];
+      {
+        const uint16_t* qrow0 = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride +
+                                static_cast<int64_t>(kv_head * G + row) * D;
+        const uint16_t* qrow1 = qrow0 + 8 * D;
+        const bool v0 = row < G, v1 = !kG8 && (row + 8 < G);
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks) {
+          uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+          if constexpr (!kFp8) {
+            if (v0) {
+              a0 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 2 * qd);
+              a2 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 8 + 2 * qd);
+            }
+            if (v1) {
+              a1 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 2 * qd);
+              a3 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 8 + 2 * qd);
+            }
+          } else {
+            // fp8 K: a thread's ldmatrix register holds d = 16*ks + 4*qd + {0,1,2,3}; the
+            // contraction index is permuted identically on the Q side.
+            if (v0) {
+              const uint2 t = *reinterpret_cast<const uint2*>(qrow0 + ks * 16 + 4 * qd);
+              a0 = t.x; a2 = t.y;
+            }
+            if (v1) {
+              const uint2 t = *reinterpret_cast<const uint2*>(qrow1 + ks * 16 + 4 * qd);
+              a1 = t.x; a3 = t.y;
+            }
+            if constexpr (kQBf16) {  // bf16 -> f16 (saturating), the MMA runs in f16 for fp8 KV
+              auto cv = [](uint32_t x) {
+                const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
+                const float l2 = fminf(fmaxf(lo, -65504.f), 65504.f), h2 = fminf(fmaxf(hi, -65504.f), 65504.f);
+                return pack2<false>(l2, h2);
+              };
+              a0 = cv(a0); a1 = cv(a1); a2 = cv(a2); a3 = cv(a3);
+            }
+          }
+          qa[ks][0] = a0; qa[ks][1] = a1; qa[ks][2] = a2; qa[ks][3] = a3;
+        }
+      }
+
+      float o[NBLK][4];
+#pragma unroll
+      for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
+      float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+      for (int t = 0; t < ntiles; ++t) {
+        cp_async_wait<NSTAGE - 2>();
+        __syncthreads();
+        issue_tile();      // refills the stage consumed in the previous iteration
+        stage_indices();   // indices for the tile after that (made visible by the next barrier)
+
+        const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
+        const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
+        const uint32_t k_s = smem_u32(stage_base + (c_count % NSTAGE) * Cfg::STAGEB);
+        const uint32_t v_s = k_s + Cfg::TILEB;
+        ++c_count;
+        if (nvalid <= 0) continue;
+
+        // ---- S = Q K^T for 16 tokens (2 n-blocks of 8)
+        float s[2][4];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+        if constexpr (!kFp8) {
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            const int mj = lane >> 3, mr = lane & 7;
+            const int tok = ts * 16 + (mj >> 1) * 8 + mr;
+            const int ch = 2 * ks + (mj & 1);
+            uint32_t r[4];
+            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+            mma_16816<kMmaBf16>(s[0], qa[ks], r[0], r[1]);
+            mma_16816<kMmaBf16>(s[1], qa[ks], r[2], r[3]);
+          }
+        } else {
+          // fp8: one 16-byte chunk = 16 d; matrices (tok 0-7, ch), (tok 8-15, ch), (tok 0-7, ch+1), (tok 8-15, ch+1)
+#pragma unroll
+          for (int kp = 0; kp < KSTEPS / 2; ++kp) {
+            const int mj = lane >> 3, mr = lane & 7;
+            const int tok = ts * 16 + (mj & 1) * 8 + mr;
+            const int ch = 2 * kp + (mj >> 1);
+            uint32_t r[4];
+            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const uint32_t r0 = r[2 * half], r1 = r[2 * half + 1];
+              const int ks = 2 * kp + half;
+              mma_16816<false>(s[0], qa[ks], e4m3x2_to_f16x2(r0 & 0xffff), e4m3x2_to_f16x2(r0 >> 16));
+              mma_16816<false>(s[1], qa[ks], e4m3x2_to_f16x2(r1 & 0xffff), e4m3x2_to_f16x2(r1 >> 16));
+            }
+          }
+        }
+
+        // ---- scale, cap, mask, online softmax (log2 domain)
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x;
+            if (p.logit_cap > 0.f) {
+              x = p.logit_cap * fast_tanh(s[nb][e] * p.scale_raw / p.logit_cap) * kLog2e;
+            } else {
+              x = s[nb][e] * p.scale_log2;
+            }
+            const int col = nb * 8 + 2 * qd + (e & 1);
+            s[nb][e] = (col < nvalid) ? x : -INFINITY;
+          }
+        }
+        float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        const float mn0 = fmaxf(m0, mx0);  // finite: at least one valid column
+        const float al0 = fast_exp2(m0 - mn0);
+        m0 = mn0;
+        float p00 = fast_exp2(s[0][0] - mn0), p01 = fast_exp2(s[0][1] - mn0);
+        float p10 = fast_exp2(s[1][0] - mn0), p11 = fast_exp2(s[1][1] - mn0);
+        l0 = l0 * al0 + (p00 + p01 + p10 + p11);
+        uint32_t pa[4];
+        pa[0] = pack2<kMmaBf16>(p00, p01);
+        pa[2] = pack2<kMmaBf16>(p10, p11);
+        float al1 = 1.f;
+        if constexpr (!kG8) {
+          float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+          const float mn1 = fmaxf(m1, mx1);
+          al1 = fast_exp2(m1 - mn1);
+          m1 = mn1;
+          const float q00 = fast_exp2(s[0][2] - mn1), q01 = fast_exp2(s[0][3] - mn1);
+          const float q10 = fast_exp2(s[1][2] - mn1), q11 = fast_exp2(s[1][3] - mn1);
+          l1 = l1 * al1 + (q00 + q01 + q10 + q11);
+          pa[1] = pack2<kMmaBf16>(q00, q01);
+          pa[3] = pack2<kMmaBf16>(q10, q11);
+        } else {
+          pa[1] = 0u; pa[3] = 0u;
+        }
+#pragma unroll
+        for (int nb = 0; nb < NBLK; ++nb) {
+          o[nb][0] *= al0; o[nb][1] *= al0;
+          if constexpr (!kG8) { o[nb][2] *= al1; o[nb][3] *= al1; }
+        }
+
+        // ---- O += P V
+        if constexpr (!kFp8) {
+#pragma unroll
+          for (int jp = 0; jp < NBLK / 2; ++jp) {
+            const int mj = lane >> 3, mr = lane & 7;
+            const int tok = ts * 16 + (mj & 1) * 8 + mr;
+            const int ch = 2 * jp + (mj >> 1);
+            uint32_t r[4];
+            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+            mma_16816<kMmaBf16>(o[2 * jp], pa, r[0], r[1]);
+            mma_16816<kMmaBf16>(o[2 * jp + 1], pa, r[2], r[3]);
+          }
+        } else {
+          // fp8 V: a transposed b16 ldmatrix hands a thread (tok 2qd, d pair), (tok 2qd+1, d pair);
+          // regroup bytes so each half-word is one d for two consecutive tokens.
+          // chunk c (16 d) -> n-block "even d" o[4c'+..]; accumulator column order is fixed up at the store.
+#pragma unroll
+          for (int cp = 0; cp < D / 32; ++cp) {
+            const int mj = lane >> 3, mr = lane & 7;
+            const int tok = ts * 16 + (mj & 1) * 8 + mr;
+            const int ch = 2 * cp + (mj >> 1);
+            uint32_t r[4];
+            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const uint32_t lo = r[2 * half], hi = r[2 * half + 1];  // tokens 0-7, tokens 8-15
+              const uint32_t e_lo = __byte_perm(lo, 0, 0x0020), o_lo = __byte_perm(lo, 0, 0x0031);
+              const uint32_t e_hi = __byte_perm(hi, 0, 0x0020), o_hi = __byte_perm(hi, 0, 0x0031);
+              const int c = 2 * cp + half;  // 16-d chunk
+              mma_16816<false>(o[2 * c], pa, e4m3x2_to_f16x2(e_lo), e4m3x2_to_f16x2(e_hi));
+              mma_16816<false>(o[2 * c + 1], pa, e4m3x2_to_f16x2(o_lo), e4m3x2_to_f16x2(o_hi));
+            }
+          }
+        }
+      }  // tiles
+
+      // ---- finish the piece: reduce l over the quad, merge the TS warps of a head, store
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      if constexpr (!kG8) {
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      }
+      if constexpr (TS > 1) {
+        // tree merge: in each round the upper half of the token sub-tiles hands its state to the lower half
+        constexpr int RSTRIDE = D + 2;
+        // the stage consumed last is free until the next issue_tile(), which sits behind a barrier
+        float* red = Cfg::RED_ALIAS
+                         ? reinterpret_cast<float*>(stage_base + ((c_count + NSTAGE - 1) % NSTAGE) * Cfg::STAGEB)
+                         : reinterpret_cast<float*>(smem + NSTAGE * Cfg::STAGEB + Cfg::IDXB);
+#pragma unroll
+        for (int half = TS / 2; half >= 1; half >>= 1) {
+          __syncthreads();
+          if (ts >= half && ts < 2 * half) {
+            float* dst = red + ((ts - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+#pragma unroll
+            for (int nb = 0; nb < NBLK; ++nb) {
+              *reinterpret_cast<float2*>(dst + row * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][0], o[nb][1]);
+              if constexpr (!kG8)
+                *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][2], o[nb][3]);
+            }
+            if (qd == 0) {
+              *reinterpret_cast<float2*>(dst + row * RSTRIDE + D) = make_float2(m0, l0);
+              if constexpr (!kG8) *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + D) = make_float2(m1, l1);
+            }
+          }
+          __syncthreads();
+          if (ts < half) {
+            const float* src = red + (ts * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+            {
+              const float2 ml = *reinterpret_cast<const float2*>(src + row * RSTRIDE + D);
+              const float mn = fmaxf(m0, ml.x);
+              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m0 - mn);
+              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
+              m0 = mn; l0 = l0 * a + ml.y * b;
+#pragma unroll
+              for (int nb = 0; nb < NBLK; ++nb) {
+                const float2 x = *reinterpret_cast<const float2*>(src + row * RSTRIDE + nb * 8 + 2 * qd);
+                o[nb][0] = o[nb][0] * a + x.x * b;
+                o[nb][1] = o[nb][1] * a + x.y * b;
+              }
+            }
+            if constexpr (!kG8) {
+              const float2 ml = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + D);
+              const float mn = fmaxf(m1, ml.x);
+              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m1 - mn);
+              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
+              m1 = mn; l1 = l1 * a + ml.y * b;
+#pragma unroll
+              for (int nb = 0; nb < NBLK; ++nb) {
+                const float2 x = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + nb * 8 + 2 * qd);
+                o[nb][2] = o[nb][2] * a + x.x * b;
+                o[nb][3] = o[nb][3] * a + x.y * b;
+              }
+            }
+          }
+        }
+      }
+
+      if (ts == 0) {
+#pragma unroll
+        for (int rr = 0; rr < (kG8 ? 1 : 2); ++rr) {
+          const int r = row + rr * 8;
+          if (r >= G) continue;
+          const float m = rr ? m1 : m0, l = rr ? l1 : l0;
+          const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
+          const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+          const int head = kv_head * G + r;
+          if (seg.slot < 0) {
+            uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
+                            static_cast<int64_t>(head) * D;
+            if constexpr (!kFp8) {
+#pragma unroll
+              for (int nb = 0; nb < NBLK; ++nb)
+                *reinterpret_cast<uint32_t*>(dst + nb * 8 + 2 * qd) =
+                    pack2<kQBf16>(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
+            } else {
+#pragma unroll
+              for (int c = 0; c < D / 16; ++c) {  // thread holds d = 16c + 4qd + {0,2} (even blk), {1,3} (odd blk)
+                const uint32_t w0 = pack2<kQBf16>(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv);
+                const uint32_t w1 = pack2<kQBf16>(o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
+                *reinterpret_cast<uint2*>(dst + c * 16 + 4 * qd) = make_uint2(w0, w1);
+              }
+            }
+            if (p.lse_out != nullptr && qd == 0) p.lse_out[static_cast<int64_t>(seg.batch) * p.Hq + head] = lse;
+          } else {
+            float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D;
+            if constexpr (!kFp8) {
+#pragma unroll
+              for (int nb = 0; nb < NBLK; ++nb)
+                *reinterpret_cast<float2*>(dst + nb * 8 + 2 * qd) =
+                    make_float2(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
+            } else {
+#pragma unroll
+              for (int c = 0; c < D / 16; ++c)
+                *reinterpret_cast<float4*>(dst + c * 16 + 4 * qd) =
+                    make_float4(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv,
+                                o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
+            }
+            if (qd == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
+          }
+        }
+      }
+    }  // segments
+    cp_async_wait<0>();
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// LSE merge of the pieces of every request that was cut across CTAs
+// (reference: triton_ops/decode_attention.py:492-552, sgl-kernel/csrc/cpu/decode.cpp:812-860).
+// One warp per (request, q head).
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= p.bs * p.Hq) return;
+  const int i = warp / p.Hq, head = warp % p.Hq;
+  const int32_t* plan = p.plan;
+  const int W = plan[kPlanUnitsPerCta];
+  const int32_t* cum = plan + kPlanHeader;
+  const int c0 = cum[i], c1 = cum[i + 1];
+  uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + static_cast<int64_t>(head) * D;
+  constexpr int EPL = D / 32;  // elements per lane
+  if (c1 == c0) {  // empty request: defined as zeros
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
+    if (p.lse_out != nullptr && lane == 0) p.lse_out[static_cast<int64_t>(i) * p.Hq + head] = -INFINITY;
+    return;
+  }
+  const int cta0 = c0 / W, cta1 = (c1 - 1) / W;
+  const int n = cta1 - cta0 + 1;
+  if (n == 1) return;  // written directly by the decode kernel
+  auto slot_of = [&](int k) { return k == 0 ? 2 * cta0 + 1 : 2 * (cta0 + k); };
+  float mx = -INFINITY;
+  for (int k = lane; k < n; k += 32) mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+  float acc[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+  float wsum = 0.f;
+  for (int k = 0; k < n; ++k) {
+    const int64_t slot = slot_of(k);
+    const float lse = p.ws_lse[slot * p.Hq + head];
+    const float w = (lse == -INFINITY) ? 0.f : __expf(lse - mx);
+    const float* src = p.ws_o + (slot * p.Hq + head) * D + lane * EPL;
+    if constexpr (EPL == 4) {
+      const float4 x = *reinterpret_cast<const float4*>(src);
+      acc[0] += w * x.x; acc[1] += w * x.y; acc[2] += w * x.z; acc[3] += w * x.w;
+    } else {
+      const float2 x = *reinterpret_cast<const float2*>(src);
+      acc[0] += w * x.x; acc[1] += w * x.y;
+    }
+    wsum += w;
+  }
+  const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+#pragma unroll
+  for (int e = 0; e < EPL; e += 2)
+    *reinterpret_cast<uint32_t*>(dst + lane * EPL + e) = pack2<kBf16>(acc[e] * inv, acc[e + 1] * inv);
+  if (p.lse_out != nullptr && lane == 0)
+    p.lse_out[static_cast<int64_t>(i) * p.Hq + head] = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
+}
+
+// ---------------------------------------------------------------------------------------
+template <int D, int HB, int KVB, bool kQBf16, bool kG8>
+static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
+  // ~192 KiB of staging per SM: 3 stages of 64 KiB (D=128 bf16) or 6 stages of 32/16 KiB
+  constexpr int NSTAGE = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
+  auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    configured = true;
+  }
+  dim3 grid(p.n_ctas, head_groups, 1);
+  kern<<<grid, kDecodeThreads, Cfg::SMEM, st>>>(p);
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
+}
+
+template <int D, int KVB, bool kQBf16, bool kG8>
+static int dispatch_hb(const DecodeParams& p, int Hkv, cudaStream_t st) {
+  if (Hkv % 8 == 0) return launch_decode<D, 8, KVB, kQBf16, kG8>(p, Hkv / 8, st);
+  if (Hkv % 4 == 0) return launch_decode<D, 4, KVB, kQBf16, kG8>(p, Hkv / 4, st);
+  if (Hkv % 2 == 0) return launch_decode<D, 2, KVB, kQBf16, kG8>(p, Hkv / 2, st);
+  return launch_decode<D, 1, KVB, kQBf16, kG8>(p, Hkv, st);
+}
+
+template <int D, int KVB>
+static int dispatch_q(const DecodeParams& p, int Hkv, bool q_bf16, cudaStream_t st) {
+  const bool g8 = p.G <= 8;
+  if (q_bf16) return g8 ? dispatch_hb<D, KVB, true, true>(p, Hkv, st) : dispatch_hb<D, KVB, true, false>(p, Hkv, st);
+  return g8 ? dispatch_hb<D, KVB, false, true>(p, Hkv, st) : dispatch_hb<D, KVB, false, false>(p, Hkv, st);
+}
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" B2_EXPORT size_t b200attn_decode_workspace_bytes(int n_ctas, int Hq, int Dv) {
+  if (n_ctas <= 0 || Hq <= 0 || Dv <= 0) return 0;
+  return static_cast<size_t>(2) * n_ctas * Hq * (static_cast<size_t>(Dv) + 1) * sizeof(float);
+}
+
+extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                               const int32_t* req_to_token, int64_t table_stride,
+                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
+                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
+                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
+                               b200attn_stream_t stream) {
+  B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0, B200ATTN_ERR_INVALID, "decode: bad sizes bs=%d Hq=%d Hkv=%d", bs, Hq, Hkv);
+  if (bs == 0) return B200ATTN_OK;
+  B2_REQUIRE(q && out && k_pool && v_pool && req_to_token && req_pool_indices && seq_lens && plan && workspace,
+             B200ATTN_ERR_INVALID, "decode: null pointer");
+  B2_REQUIRE(Hq % Hkv == 0, B200ATTN_ERR_INVALID, "decode: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
+  const int G = Hq / Hkv;
+  B2_REQUIRE(G <= 16, B200ATTN_ERR_UNSUPPORTED, "decode: GQA group %d > 16 is not built", G);
+  B2_REQUIRE(D == 64 || D == 128, B200ATTN_ERR_UNSUPPORTED, "decode: head dim %d (64/128 only)", D);
+  B2_REQUIRE(q_dtype == B200ATTN_BF16 || q_dtype == B200ATTN_F16, B200ATTN_ERR_UNSUPPORTED, "decode: q dtype %d", q_dtype);
+  B2_REQUIRE(kv_dtype == q_dtype || kv_dtype == B200ATTN_FP8_E4M3, B200ATTN_ERR_UNSUPPORTED,
+             "decode: kv dtype %d with q dtype %d", kv_dtype, q_dtype);
+  const int kvb = elem_size(kv_dtype);
+  B2_REQUIRE(aligned16(q) && aligned16(out) && aligned16(k_pool) && aligned16(v_pool) && q_tok_stride % 8 == 0 &&
+                 out_tok_stride % 8 == 0 && (pool_tok_stride * kvb) % 16 == 0,
+             B200ATTN_ERR_INVALID, "decode: tensors must be 16-byte aligned");
+  B2_REQUIRE(pool_tok_stride >= static_cast<int64_t>(Hkv) * D, B200ATTN_ERR_INVALID, "decode: pool_tok_stride < Hkv*D");
+  B2_REQUIRE(n_ctas > 0, B200ATTN_ERR_INVALID, "decode: n_ctas=%d", n_ctas);
+  B2_REQUIRE(workspace_bytes >= b200attn_decode_workspace_bytes(n_ctas, Hq, D), B200ATTN_ERR_WORKSPACE,
+             "decode: workspace %zu < %zu bytes", workspace_bytes, b200attn_decode_workspace_bytes(n_ctas, Hq, D));
+  B2_REQUIRE(k_scale > 0.f && v_scale > 0.f, B200ATTN_ERR_INVALID, "decode: k_scale/v_scale must be > 0");
+
+  DecodeParams p;
+  p.q = q; p.out = out; p.k_pool = k_pool; p.v_pool = v_pool;
+  p.req_to_token = req_to_token; p.req_pool_indices = req_pool_indices; p.seq_lens = seq_lens;
+  p.plan = plan;
+  p.ws_o = reinterpret_cast<float*>(workspace);
+  p.ws_lse = p.ws_o + static_cast<size_t>(2) * n_ctas * Hq * D;
+  p.lse_out = lse_out;
+  p.q_tok_stride = q_tok_stride; p.out_tok_stride = out_tok_stride;
+  p.pool_tok_stride = pool_tok_stride; p.table_stride = table_stride;
+  p.idx_is_i64 = idx_is_i64;
+  p.bs = bs; p.Hq = Hq; p.Hkv = Hkv; p.G = G;
+  p.n_ctas = n_ctas;
+  p.scale_raw = sm_scale * k_scale;
+  p.scale_log2 = sm_scale * k_scale * kLog2e;
+  p.logit_cap = logit_cap;
+  p.v_scale = v_scale;
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool q_bf16 = q_dtype == B200ATTN_BF16;
+  int rc;
+  if (D == 128) rc = (kvb == 2) ? dispatch_q<128, 2>(p, Hkv, q_bf16, st) : dispatch_q<128, 1>(p, Hkv, q_bf16, st);
+  else rc = (kvb == 2) ? dispatch_q<64, 2>(p, Hkv, q_bf16, st) : dispatch_q<64, 1>(p, Hkv, q_bf16, st);
+  if (rc != B200ATTN_OK) return rc;
+
+  const int warps = bs * Hq;
+  const int blocks = (warps * 32 + 127) / 128;
+  if (D == 128) {
+    if (q_bf16) decode_merge_kernel<128, true><<<blocks, 128, 0, st>>>(p);
+    else decode_merge_kernel<128, false><<<blocks, 128, 0, st>>>(p);
+  } else {
+    if (q_bf16) decode_merge_kernel<64, true><<<blocks, 128, 0, st>>>(p);
+    else decode_merge_kernel<64, false><<<blocks, 128, 0, st>>>(p);
+  }
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
+}

@@ -1,0 +1,233 @@
+"""Tensor-level wrappers over the C ABI: torch supplies device memory and streams only.
+
+Every function validates dtypes/devices, passes raw pointers + strides to
+`libb200attn.so`, and raises `B200AttnError` on a non-zero return code.
+"""
+from __future__ import annotations
+
+from typing import Optional, Union
+
+import torch
+
+from . import _lib
+from ._lib import B200AttnError, check
+
+_DT = {torch.bfloat16: _lib.BF16, torch.float16: _lib.F16, torch.float32: _lib.F32,
+       torch.float8_e4m3fn: _lib.FP8_E4M3}
+
+
+def _dt(t: torch.dtype) -> int:
+    if t not in _DT:
+        raise B200AttnError(f"unsupported dtype {t}")
+    return _DT[t]
+
+
+def _ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def _cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise B200AttnError("b200attn operates on CUDA tensors only (no CPU fallback exists)")
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _is_i64(t: torch.Tensor) -> int:
+    if t.dtype == torch.int64:
+        return 1
+    if t.dtype == torch.int32:
+        return 0
+    raise B200AttnError(f"index tensor must be int32 or int64, got {t.dtype}")
+
+
+def _pool_dtype(pool: torch.Tensor, logical: Optional[torch.dtype]) -> int:
+    """MHATokenToKVPool stores fp8 as uint8 (`store_dtype`, memory_pool.py:146-150)."""
+    if pool.dtype == torch.uint8:
+        if logical not in (None, torch.float8_e4m3fn):
+            raise B200AttnError(f"uint8 pool with logical dtype {logical} (only float8_e4m3fn is built)")
+        return _lib.FP8_E4M3
+    return _dt(pool.dtype)
+
+
+def _last_dim_contig(t: torch.Tensor, name: str) -> None:
+    if t.stride(-1) != 1:
+        raise B200AttnError(f"{name}: last dimension must be contiguous")
+
+
+ScaleT = Union[None, float, torch.Tensor]
+
+
+def _scale_args(s: ScaleT):
+    """-> (host float, device tensor or None, n). 0.0 host scale means 'no scaling'."""
+    if s is None:
+        return 0.0, None, 1
+    if isinstance(s, torch.Tensor):
+        if s.is_cuda:
+            t = s.detach().to(torch.float32).reshape(-1).contiguous()
+            return 0.0, t, t.numel()
+        return float(s), None, 1
+    return float(s), None, 1
+
+
+def kv_write(k: torch.Tensor, v: torch.Tensor, loc: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+             k_scale: ScaleT = None, v_scale: ScaleT = None, pool_dtype: Optional[torch.dtype] = None,
+             scale_mode: int = _lib.SCALE_DIV, writeback_scaled: bool = False) -> None:
+    """pool[loc] = cast(k), cast(v): MHATokenToKVPool.set_kv_buffer (memory_pool.py:420-458)."""
+    _cuda(k, v, loc, k_pool, v_pool)
+    if k.dim() != 3 or v.shape != k.shape:
+        raise B200AttnError(f"kv_write: k/v must be [T,Hkv,D] of equal shape, got {tuple(k.shape)} {tuple(v.shape)}")
+    T, H, D = k.shape
+    if loc.dtype != torch.int64 or loc.numel() != T or not loc.is_contiguous():
+        raise B200AttnError("kv_write: loc must be a contiguous int64 [T] tensor")
+    _last_dim_contig(k, "k"); _last_dim_contig(v, "v")
+    if k_pool.dim() != 3 or k_pool.shape[1:] != (H, D) or v_pool.shape != k_pool.shape:
+        raise B200AttnError("kv_write: pool must be [P,Hkv,D]")
+    if k_pool.stride(2) != 1 or k_pool.stride(1) != D:
+        raise B200AttnError("kv_write: pool head/dim strides must be (D, 1)")
+    ks_h, ks_d, n1 = _scale_args(k_scale)
+    vs_h, vs_d, n2 = _scale_args(v_scale)
+    keep = (ks_d, vs_d)  # keep temporaries alive until the launch is enqueued
+    check(_lib.load().b200attn_kv_write(
+        k.data_ptr(), v.data_ptr(), k.stride(0), k.stride(1), v.stride(0), v.stride(1), loc.data_ptr(),
+        T, H, D, k_pool.data_ptr(), v_pool.data_ptr(), k_pool.stride(0), _dt(k.dtype),
+        _pool_dtype(k_pool, pool_dtype), ks_h, vs_h, _ptr(ks_d), _ptr(vs_d), max(n1, n2),
+        int(scale_mode), int(bool(writeback_scaled)), _stream(k)), "b200attn_kv_write")
+    del keep
+
+
+def decode_plan_bytes(max_bs: int, n_ctas: int) -> int:
+    return _lib.load().b200attn_decode_plan_bytes(int(max_bs), int(n_ctas))
+
+
+def decode_workspace_bytes(n_ctas: int, Hq: int, Dv: int) -> int:
+    return _lib.load().b200attn_decode_workspace_bytes(int(n_ctas), int(Hq), int(Dv))
+
+
+def decode_plan(seq_lens: torch.Tensor, n_ctas: int, plan: torch.Tensor, min_units_per_cta: int = 4) -> None:
+    _cuda(seq_lens, plan)
+    if plan.dtype != torch.int32 or not plan.is_contiguous():
+        raise B200AttnError("decode_plan: plan must be a contiguous int32 tensor")
+    check(_lib.load().b200attn_decode_plan(
+        seq_lens.data_ptr(), _is_i64(seq_lens), seq_lens.numel(), int(n_ctas), int(min_units_per_cta),
+        plan.data_ptr(), plan.numel() * 4, _stream(plan)), "b200attn_decode_plan")
+
+
+def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+           req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+           plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
+           k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
+           lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q,out [bs,Hq,D]; pools [P,Hkv,D]; see b200attn_decode in include/b200attn.h."""
+    _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, workspace, lse_out)
+    bs, Hq, D = q.shape
+    Hkv = k_pool.shape[1]
+    if out.shape != q.shape or out.dtype != q.dtype:
+        raise B200AttnError("decode: out must match q")
+    if q.stride(2) != 1 or q.stride(1) != D or out.stride(2) != 1 or out.stride(1) != D:
+        raise B200AttnError("decode: q/out head stride must be D")
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise B200AttnError("decode: req_to_token must be int32 with contiguous rows")
+    if req_pool_indices.dtype != seq_lens.dtype:
+        raise B200AttnError("decode: req_pool_indices and seq_lens must share a dtype")
+    if k_pool.stride(1) != D or k_pool.stride(2) != 1 or v_pool.stride() != k_pool.stride():
+        raise B200AttnError("decode: pool must be [P,Hkv,D] with strides (*, D, 1)")
+    if lse_out is not None and (lse_out.dtype != torch.float32 or not lse_out.is_contiguous()):
+        raise B200AttnError("decode: lse_out must be contiguous fp32 [bs,Hq]")
+    check(_lib.load().b200attn_decode(
+        q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+        k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+        seq_lens.data_ptr(), _is_i64(seq_lens), bs, Hq, Hkv, D, _dt(q.dtype), _pool_dtype(k_pool, kv_dtype),
+        float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale), plan.data_ptr(), int(n_ctas),
+        workspace.data_ptr(), workspace.numel() * workspace.element_size(), _ptr(lse_out), _stream(q)),
+        "b200attn_decode")
+    return out
+
+
+def merge_state(a: torch.Tensor, lse_a: torch.Tensor, b: torch.Tensor, lse_b: torch.Tensor,
+                out: Optional[torch.Tensor] = None, out_lse: Optional[torch.Tensor] = None):
+    """merge_state / merge_state_v2 (layers/attention/merge_state.py:26-46)."""
+    _cuda(a, lse_a, b, lse_b, out, out_lse)
+    if a.dim() != 3 or a.shape != b.shape or a.dtype != b.dtype:
+        raise B200AttnError("merge_state: a,b must be [T,H,D] of equal shape/dtype")
+    T, H, D = a.shape
+    a, b = a.contiguous(), b.contiguous()
+    lse_a = lse_a.to(torch.float32).contiguous(); lse_b = lse_b.to(torch.float32).contiguous()
+    if out is None:
+        out = torch.empty_like(a)
+    if out_lse is None:
+        out_lse = torch.empty((T, H), dtype=torch.float32, device=a.device)
+    if not out.is_contiguous() or not out_lse.is_contiguous():
+        raise B200AttnError("merge_state: outputs must be contiguous")
+    check(_lib.load().b200attn_merge_state(
+        a.data_ptr(), lse_a.data_ptr(), b.data_ptr(), lse_b.data_ptr(), out.data_ptr(), out_lse.data_ptr(),
+        T, H, D, _dt(a.dtype), _stream(a)), "b200attn_merge_state")
+    return out, out_lse
+
+
+def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+           req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+           extend_seq_lens: torch.Tensor, extend_prefix_lens: torch.Tensor, extend_start_loc: torch.Tensor,
+           max_extend_len: int, sm_scale: float, logit_cap: float = 0.0, k_scale: float = 1.0,
+           v_scale: float = 1.0, causal: bool = True, kv_dtype: Optional[torch.dtype] = None,
+           impl: int = _lib.EXTEND_AUTO) -> torch.Tensor:
+    """q,out [T,Hq,D]; see b200attn_extend in include/b200attn.h."""
+    _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, extend_seq_lens,
+          extend_prefix_lens, extend_start_loc)
+    T, Hq, D = q.shape
+    Hkv = k_pool.shape[1]
+    bs = seq_lens.numel()
+    if out.shape != q.shape or out.dtype != q.dtype:
+        raise B200AttnError("extend: out must match q")
+    if q.stride(2) != 1 or q.stride(1) != D or out.stride(2) != 1 or out.stride(1) != D:
+        raise B200AttnError("extend: q/out head stride must be D")
+    for name, t in (("extend_seq_lens", extend_seq_lens), ("extend_prefix_lens", extend_prefix_lens),
+                    ("extend_start_loc", extend_start_loc)):
+        if t.dtype != torch.int32 or not t.is_contiguous() or t.numel() != bs:
+            raise B200AttnError(f"extend: {name} must be contiguous int32 [bs]")
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise B200AttnError("extend: req_to_token must be int32 with contiguous rows")
+    if req_pool_indices.dtype != seq_lens.dtype:
+        raise B200AttnError("extend: req_pool_indices and seq_lens must share a dtype")
+    check(_lib.load().b200attn_extend(
+        q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+        k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+        seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
+        extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
+        _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
+        int(bool(causal)), int(impl), _stream(q)), "b200attn_extend")
+    return out
+
+
+def flatten_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, lens: torch.Tensor,
+                       kv_indptr: torch.Tensor, kv_start: Optional[torch.Tensor], kv_indices: torch.Tensor) -> None:
+    """create_flashinfer_kv_indices_triton (layers/attention/utils.py:5-41)."""
+    _cuda(req_to_token, req_pool_indices, lens, kv_indptr, kv_start, kv_indices)
+    if req_to_token.dtype != torch.int32 or kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
+        raise B200AttnError("flatten_kv_indices: table, kv_indptr and kv_indices must be int32")
+    if lens.dtype != req_pool_indices.dtype or (kv_start is not None and kv_start.dtype != lens.dtype):
+        raise B200AttnError("flatten_kv_indices: req_pool_indices, lens and kv_start must share a dtype")
+    check(_lib.load().b200attn_flatten_kv_indices(
+        req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(), lens.data_ptr(),
+        _ptr(kv_start), _is_i64(lens), kv_indptr.data_ptr(), kv_indices.data_ptr(), lens.numel(),
+        _stream(req_to_token)), "b200attn_flatten_kv_indices")
+
+
+def gather_kv(pool: torch.Tensor, indices: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[j] = pool[indices[j]] -- the page gather `k_cache[per_req_tokens]`, bit exact."""
+    _cuda(pool, indices, out)
+    if indices.dtype != torch.int32 or not indices.is_contiguous():
+        raise B200AttnError("gather_kv: indices must be contiguous int32")
+    row = pool[0]
+    if not row.is_contiguous():
+        raise B200AttnError("gather_kv: pool rows must be contiguous")
+    if out is None:
+        out = torch.empty((indices.numel(),) + tuple(pool.shape[1:]), dtype=pool.dtype, device=pool.device)
+    row_bytes = row.numel() * pool.element_size()
+    check(_lib.load().b200attn_gather_kv(
+        pool.data_ptr(), pool.stride(0) * pool.element_size(), indices.data_ptr(), indices.numel(), row_bytes,
+        out.data_ptr(), _stream(pool)), "b200attn_gather_kv")
+    return out
