@@ -14,7 +14,8 @@
  *                                get_num_kv_splits_triton) -- device-only, CUDA-graph safe
  *   b200attn_decode              layers/attention/torch_native_backend.py:112-180,226-267 (oracle),
  *                                triton_ops/decode_attention.py:677-728, sgl-kernel/csrc/cpu/decode.cpp:1375
- *   b200attn_decode (merge part) triton_ops/decode_attention.py:492-552, decode.cpp:812-860
+ *   b200attn_decode_partial      stage 1 of the above (triton_ops/decode_attention.py:555-609)
+ *   b200attn_decode_merge        triton_ops/decode_attention.py:492-552,611-674, decode.cpp:812-860
  *   b200attn_merge_state         layers/attention/merge_state.py:26-46,
  *                                sgl-kernel/csrc/attention/merge_attn_states.cu:32-106
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
@@ -136,6 +137,21 @@ int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_
                     const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
                     float* lse_out, b200attn_stream_t stream);
 
+/* The two stages of b200attn_decode, separately launchable (the reference's Triton backend exposes its
+ * stage 1 / stage 2 the same way: decode_attention.py:555-609 `_decode_att_m_fwd`, :611-674
+ * `_decode_softmax_reducev_fwd`).  b200attn_decode == partial followed by merge on the same stream.
+ * b200attn_decode_partial takes exactly the arguments of b200attn_decode. */
+int b200attn_decode_partial(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                            const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                            const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                            const void* seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype,
+                            int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
+                            const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
+                            float* lse_out, b200attn_stream_t stream);
+int b200attn_decode_merge(void* out, int64_t out_tok_stride, int bs, int Hq, int D, int q_dtype,
+                          const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
+                          float* lse_out, b200attn_stream_t stream);
+
 /* ---------------------------------------------------------------- 2-way LSE merge
  * out = (e^{la-m} a + e^{lb-m} b) / (e^{la-m} + e^{lb-m}),  lse = log(sum) + m, m = max(la, lb);
  * +inf LSE is treated as -inf (merge_attn_states.cu:47-50).
@@ -154,14 +170,15 @@ int b200attn_merge_state(const void* a, const float* lse_a, const void* b, const
  *   extend_start_loc [bs] int32 (row of request i's first query in q/out)
  *   seq_lens[i] must equal P_i + E_i.
  *   key j of request i is visible to its query t iff j <= P_i + t (causal != 0), else all keys.
- *   max_extend_len: upper bound of E_i known on the host (grid sizing, no device sync). */
+ *   max_extend_len: upper bound of E_i known on the host (grid sizing, no device sync).
+ *   lse_out: optional fp32 [T, Hq] natural-log LSE of every (query, head), or NULL. */
 int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
                     const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
                     const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
                     const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
                     const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
                     int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
-                    float logit_cap, float k_scale, float v_scale, int causal, int impl,
+                    float logit_cap, float k_scale, float v_scale, int causal, int impl, float* lse_out,
                     b200attn_stream_t stream);
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */

@@ -1,0 +1,241 @@
+"""B200AttnBackend: the SGLang AttentionBackend whose hot path is libb200attn.so.
+
+Mirrors the reference interface one to one (python/sglang/srt/layers/attention/...):
+  AttentionBackend ABC                      base_attn_backend.py:14-115
+  constructor / attributes read             triton_backend.py:41-122
+  init_forward_metadata                     triton_backend.py:160-336   (here: one device-side plan kernel)
+  forward_decode / forward_extend           triton_backend.py:632-732, torch_native_backend.py:182-267
+  CUDA-graph hooks                          triton_backend.py:338-630, cuda_graph_runner.py:251-256,550-558,686-695
+KV write semantics: mem_cache/memory_pool.py:420-458 (the backend owns that call, as
+triton_backend.py:647-650,706-709 do), done by the b200attn KV-write kernel.
+
+There is no fallback path: a missing library or an unsupported feature raises.
+"""
+from __future__ import annotations
+
+from abc import ABC, abstractmethod
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib, ops
+from ._lib import B200AttnError
+
+
+class AttentionBackend(ABC):
+    """Same surface as the reference's base class (base_attn_backend.py:14-115)."""
+
+    @abstractmethod
+    def init_forward_metadata(self, forward_batch):
+        raise NotImplementedError()
+
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        raise NotImplementedError()
+
+    def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens, encoder_lens,
+                                                 forward_mode, spec_info):
+        raise NotImplementedError()
+
+    def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens,
+                                                forward_mode, spec_info, seq_lens_cpu):
+        raise NotImplementedError()
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        raise NotImplementedError()
+
+    def forward(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+        if forward_batch.forward_mode.is_decode():
+            return self.forward_decode(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache, **kwargs)
+        return self.forward_extend(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache, **kwargs)
+
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        raise NotImplementedError()
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        raise NotImplementedError()
+
+    def support_triton(self):
+        return True
+
+
+@dataclass
+class ForwardMetadata:
+    is_decode: bool
+    bs: int
+    req_pool_indices: Optional[torch.Tensor] = None  # set only by the CUDA-graph hooks (fixed buffers)
+    seq_lens: Optional[torch.Tensor] = None
+    extend_start_loc: Optional[torch.Tensor] = None
+    max_extend_len: int = 0
+
+
+class B200AttnBackend(AttentionBackend):
+    def __init__(self, model_runner, skip_prefill: bool = False):
+        super().__init__()
+        lib = _lib.load()  # raises if libb200attn.so is missing: there is no other implementation
+        self.device = model_runner.device
+        if not str(self.device).startswith("cuda"):
+            raise B200AttnError("B200AttnBackend needs a CUDA device (sm_100a); there is no CPU path")
+        info = _lib.device_info()
+        if info["cc_major"] != 10:
+            raise B200AttnError(f"libb200attn.so is built for sm_100a only, found compute capability "
+                                f"{info['cc_major']}.{info['cc_minor']}")
+        self.skip_prefill = skip_prefill
+        sw = getattr(model_runner, "sliding_window_size", None)
+        if sw is not None and sw > 0:
+            raise NotImplementedError("b200 attention backend: sliding-window attention is not built")
+        if getattr(model_runner.model_config, "is_encoder_decoder", False):
+            raise NotImplementedError("b200 attention backend: encoder-decoder (cross attention) is not built")
+
+        self.req_to_token = model_runner.req_to_token_pool.req_to_token
+        self.max_bs = model_runner.req_to_token_pool.size
+        self.max_context_len = model_runner.model_config.context_len
+        tp = getattr(model_runner, "tp_size", 1)
+        self.num_head = model_runner.model_config.num_attention_heads // tp
+        self.num_kv_head = model_runner.model_config.get_num_kv_heads(tp)
+        pool = model_runner.token_to_kv_pool
+        self.v_head_dim = pool.get_value_buffer(getattr(pool, "start_layer", 0)).shape[-1]
+        self.kv_dtype = pool.dtype
+        self.page_size = getattr(model_runner, "page_size", 1)
+
+        # persistent decode grid: one CTA per SM (the decode kernel keeps ~190 KiB of gathers in flight per CTA)
+        self.sm_count = info["sm_count"]
+        self.n_ctas = self.sm_count
+        self.min_units_per_cta = 4
+        self._alloc_decode_buffers(self.max_bs)
+        self.forward_metadata: Optional[ForwardMetadata] = None
+        self.scale_mode = _lib.SCALE_DIV
+        self.writeback_scaled_kv = False
+
+    # ------------------------------------------------------------------ buffers
+    def _alloc_decode_buffers(self, max_bs: int) -> None:
+        self.plan = torch.zeros(ops.decode_plan_bytes(max_bs, self.n_ctas) // 4, dtype=torch.int32, device=self.device)
+        ws = ops.decode_workspace_bytes(self.n_ctas, self.num_head, self.v_head_dim)
+        self.workspace = torch.empty(ws // 4, dtype=torch.float32, device=self.device)
+
+    # ------------------------------------------------------------------ metadata
+    def init_forward_metadata(self, forward_batch):
+        """One tiny device-side kernel (decode) or nothing at all (extend): no flattened kv_indices
+        copy, no host sync (the reference syncs on max_extend_len, triton_backend.py:320)."""
+        if getattr(forward_batch, "spec_info", None) is not None:
+            raise NotImplementedError("b200 attention backend: speculative decoding (spec_info) is not built")
+        bs = forward_batch.batch_size
+        mode = forward_batch.forward_mode
+        if mode.is_decode_or_idle():
+            if bs > 0:
+                ops.decode_plan(forward_batch.seq_lens, self.n_ctas, self.plan, self.min_units_per_cta)
+            self.forward_metadata = ForwardMetadata(True, bs)
+            return
+        ext_cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
+        if ext_cpu is not None:
+            max_extend = max(ext_cpu) if len(ext_cpu) else 0
+        else:  # the reference's own (syncing) way, triton_backend.py:320
+            max_extend = int(forward_batch.extend_seq_lens.max().item()) if bs else 0
+        start = getattr(forward_batch, "extend_start_loc", None)
+        if start is None and bs:
+            ext = forward_batch.extend_seq_lens
+            start = (torch.cumsum(ext, 0) - ext).to(torch.int32)
+        self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend)
+
+    # ------------------------------------------------------------------ CUDA graphs
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        """Fixed-address plan/workspace buffers for capture + replay (triton_backend.py:338-388)."""
+        if max_bs > self.max_bs:
+            self.max_bs = max_bs
+            self._alloc_decode_buffers(max_bs)
+
+    def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens, encoder_lens,
+                                                 forward_mode, spec_info):
+        if encoder_lens is not None:
+            raise NotImplementedError("b200 attention backend: encoder_lens is not supported")
+        if spec_info is not None or not forward_mode.is_decode_or_idle():
+            raise NotImplementedError("b200 attention backend: only DECODE batches run under CUDA graphs")
+        ops.decode_plan(seq_lens[:bs], self.n_ctas, self.plan, self.min_units_per_cta)
+        self.forward_metadata = ForwardMetadata(True, bs, req_pool_indices=req_pool_indices[:bs], seq_lens=seq_lens[:bs])
+
+    def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens,
+                                                forward_mode, spec_info, seq_lens_cpu):
+        """Runs right before graph.replay(): refresh the plan in place from the (device) seq_lens.
+        Padded rows arrive as seq_len = 1 / req_pool_idx = 0 (cuda_graph_runner.py:686-695)."""
+        if spec_info is not None or not forward_mode.is_decode_or_idle():
+            raise NotImplementedError("b200 attention backend: only DECODE batches run under CUDA graphs")
+        ops.decode_plan(seq_lens[:bs], self.n_ctas, self.plan, self.min_units_per_cta)
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        return 1
+
+    # ------------------------------------------------------------------ helpers
+    def _check_layer(self, layer) -> None:
+        if getattr(layer, "is_cross_attention", False):
+            raise NotImplementedError("b200 attention backend: cross attention is not built")
+        if layer.qk_head_dim != layer.v_head_dim:
+            raise NotImplementedError("b200 attention backend: qk_head_dim != v_head_dim (MLA) is not built")
+        sw = getattr(layer, "sliding_window_size", None)
+        if sw is not None and sw > -1:
+            raise NotImplementedError("b200 attention backend: sliding-window layers are not built")
+
+    @staticmethod
+    def _kv_scales(layer):
+        ks = getattr(layer, "k_scale_float", None)
+        vs = getattr(layer, "v_scale_float", None)
+        return (1.0 if ks is None else float(ks)), (1.0 if vs is None else float(vs))
+
+    def _save_kv(self, layer, forward_batch, k, v) -> None:
+        pool = forward_batch.token_to_kv_pool
+        lid = layer.layer_id - getattr(pool, "start_layer", 0)
+        k3 = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
+        v3 = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
+        # scales are only meaningful when the pool is narrower than k/v (memory_pool.py:436-442);
+        # like FlashInfer (flashinfer_backend.py:470-476) the layer's calibrated scales are applied
+        ks = getattr(layer, "k_scale", None) if getattr(layer, "k_scale", None) is not None \
+            else getattr(layer, "k_scale_float", None)
+        vs = getattr(layer, "v_scale", None) if getattr(layer, "v_scale", None) is not None \
+            else getattr(layer, "v_scale_float", None)
+        ops.set_kv_buffer(pool.k_buffer[lid], pool.v_buffer[lid], forward_batch.out_cache_loc, k3, v3, pool.dtype,
+                          ks, vs, self.scale_mode, self.writeback_scaled_kv)
+
+    # ------------------------------------------------------------------ forward
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        self._check_layer(layer)
+        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
+        o = torch.empty_like(q)
+        if save_kv_cache:
+            self._save_kv(layer, forward_batch, k, v)
+        if q.shape[0] == 0:
+            return o
+        md = self.forward_metadata
+        rpi = md.req_pool_indices if md.req_pool_indices is not None else forward_batch.req_pool_indices
+        sl = md.seq_lens if md.seq_lens is not None else forward_batch.seq_lens
+        pool = forward_batch.token_to_kv_pool
+        lid = layer.layer_id - getattr(pool, "start_layer", 0)
+        # the layer_transfer_counter wait (HiCache) lives in get_key_buffer (memory_pool.py:401-402)
+        pool.get_key_buffer(layer.layer_id)
+        k_scale, v_scale = self._kv_scales(layer)
+        ops.decode(q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+                   o.view(-1, layer.tp_q_head_num, layer.v_head_dim), pool.k_buffer[lid], pool.v_buffer[lid],
+                   forward_batch.req_to_token_pool.req_to_token, rpi, sl, self.plan, self.n_ctas, self.workspace,
+                   layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0, k_scale, v_scale, kv_dtype=pool.dtype)
+        return o
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        self._check_layer(layer)
+        o = torch.empty_like(q)
+        if save_kv_cache:
+            self._save_kv(layer, forward_batch, k, v)
+        md = self.forward_metadata
+        if md.bs == 0 or q.shape[0] == 0:
+            return o
+        from .interfaces import AttentionType  # value-compatible with the reference enum
+        attn_type = getattr(layer, "attn_type", None)
+        causal = not (attn_type is not None and getattr(attn_type, "value", attn_type) == AttentionType.ENCODER_ONLY.value)
+        pool = forward_batch.token_to_kv_pool
+        lid = layer.layer_id - getattr(pool, "start_layer", 0)
+        pool.get_key_buffer(layer.layer_id)
+        k_scale, v_scale = self._kv_scales(layer)
+        ops.extend(q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+                   o.view(-1, layer.tp_q_head_num, layer.v_head_dim), pool.k_buffer[lid], pool.v_buffer[lid],
+                   forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
+                   forward_batch.seq_lens, forward_batch.extend_seq_lens, forward_batch.extend_prefix_lens,
+                   md.extend_start_loc, md.max_extend_len, layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0,
+                   k_scale, v_scale, causal=causal, kv_dtype=pool.dtype)
+        return o

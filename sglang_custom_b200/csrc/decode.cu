@@ -604,18 +604,20 @@ extern "C" B2_EXPORT size_t b200attn_decode_workspace_bytes(int n_ctas, int Hq, 
   return static_cast<size_t>(2) * n_ctas * Hq * (static_cast<size_t>(Dv) + 1) * sizeof(float);
 }
 
-extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
-                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
-                               const int32_t* req_to_token, int64_t table_stride,
-                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
-                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
-                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
-                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
-                               b200attn_stream_t stream) {
+namespace b200attn {
+
+// argument checks shared by the three decode entry points; fills DecodeParams
+static int decode_setup(DecodeParams& p, const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                        const void* k_pool, const void* v_pool, int64_t pool_tok_stride, const int32_t* req_to_token,
+                        int64_t table_stride, const void* req_pool_indices, const void* seq_lens, int idx_is_i64,
+                        int bs, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale, float logit_cap,
+                        float k_scale, float v_scale, const int32_t* plan, int n_ctas, void* workspace,
+                        size_t workspace_bytes, float* lse_out, bool need_inputs) {
   B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0, B200ATTN_ERR_INVALID, "decode: bad sizes bs=%d Hq=%d Hkv=%d", bs, Hq, Hkv);
-  if (bs == 0) return B200ATTN_OK;
-  B2_REQUIRE(q && out && k_pool && v_pool && req_to_token && req_pool_indices && seq_lens && plan && workspace,
-             B200ATTN_ERR_INVALID, "decode: null pointer");
+  B2_REQUIRE(out && plan && workspace, B200ATTN_ERR_INVALID, "decode: null pointer");
+  if (need_inputs)
+    B2_REQUIRE(q && k_pool && v_pool && req_to_token && req_pool_indices && seq_lens, B200ATTN_ERR_INVALID,
+               "decode: null pointer");
   B2_REQUIRE(Hq % Hkv == 0, B200ATTN_ERR_INVALID, "decode: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
   const int G = Hq / Hkv;
   B2_REQUIRE(G <= 16, B200ATTN_ERR_UNSUPPORTED, "decode: GQA group %d > 16 is not built", G);
@@ -633,7 +635,6 @@ extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, vo
              "decode: workspace %zu < %zu bytes", workspace_bytes, b200attn_decode_workspace_bytes(n_ctas, Hq, D));
   B2_REQUIRE(k_scale > 0.f && v_scale > 0.f, B200ATTN_ERR_INVALID, "decode: k_scale/v_scale must be > 0");
 
-  DecodeParams p;
   p.q = q; p.out = out; p.k_pool = k_pool; p.v_pool = v_pool;
   p.req_to_token = req_to_token; p.req_pool_indices = req_pool_indices; p.seq_lens = seq_lens;
   p.plan = plan;
@@ -649,15 +650,16 @@ extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, vo
   p.scale_log2 = sm_scale * k_scale * kLog2e;
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
+  return B200ATTN_OK;
+}
 
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool q_bf16 = q_dtype == B200ATTN_BF16;
-  int rc;
-  if (D == 128) rc = (kvb == 2) ? dispatch_q<128, 2>(p, Hkv, q_bf16, st) : dispatch_q<128, 1>(p, Hkv, q_bf16, st);
-  else rc = (kvb == 2) ? dispatch_q<64, 2>(p, Hkv, q_bf16, st) : dispatch_q<64, 1>(p, Hkv, q_bf16, st);
-  if (rc != B200ATTN_OK) return rc;
+static int launch_partial(const DecodeParams& p, int D, int kvb, bool q_bf16, cudaStream_t st) {
+  if (D == 128) return (kvb == 2) ? dispatch_q<128, 2>(p, p.Hkv, q_bf16, st) : dispatch_q<128, 1>(p, p.Hkv, q_bf16, st);
+  return (kvb == 2) ? dispatch_q<64, 2>(p, p.Hkv, q_bf16, st) : dispatch_q<64, 1>(p, p.Hkv, q_bf16, st);
+}
 
-  const int warps = bs * Hq;
+static int launch_merge(const DecodeParams& p, int D, bool q_bf16, cudaStream_t st) {
+  const int warps = p.bs * p.Hq;
   const int blocks = (warps * 32 + 127) / 128;
   if (D == 128) {
     if (q_bf16) decode_merge_kernel<128, true><<<blocks, 128, 0, st>>>(p);
@@ -668,4 +670,59 @@ extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, vo
   }
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
+}
+
+}  // namespace b200attn
+
+#define B2_DECODE_ARGS                                                                                            \
+  q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token, table_stride,              \
+      req_pool_indices, seq_lens, idx_is_i64, bs, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap, k_scale,    \
+      v_scale, plan, n_ctas, workspace, workspace_bytes, lse_out
+
+extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                               const int32_t* req_to_token, int64_t table_stride,
+                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
+                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
+                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
+                               b200attn_stream_t stream) {
+  if (bs == 0) return B200ATTN_OK;
+  DecodeParams p;
+  const int rc = decode_setup(p, B2_DECODE_ARGS, true);
+  if (rc != B200ATTN_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool q_bf16 = q_dtype == B200ATTN_BF16;
+  const int rc2 = launch_partial(p, D, elem_size(kv_dtype), q_bf16, st);
+  if (rc2 != B200ATTN_OK) return rc2;
+  return launch_merge(p, D, q_bf16, st);
+}
+
+// stage 1 only: the persistent split-KV kernel (final outputs of unsplit requests + fp32 partials)
+extern "C" B2_EXPORT int b200attn_decode_partial(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                               const int32_t* req_to_token, int64_t table_stride,
+                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
+                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
+                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
+                               b200attn_stream_t stream) {
+  if (bs == 0) return B200ATTN_OK;
+  DecodeParams p;
+  const int rc = decode_setup(p, B2_DECODE_ARGS, true);
+  if (rc != B200ATTN_OK) return rc;
+  return launch_partial(p, D, elem_size(kv_dtype), q_dtype == B200ATTN_BF16, static_cast<cudaStream_t>(stream));
+}
+
+// stage 2 only: LSE merge of the partials of requests that were cut across CTAs
+extern "C" B2_EXPORT int b200attn_decode_merge(void* out, int64_t out_tok_stride, int bs, int Hq, int D, int q_dtype,
+                                               const int32_t* plan, int n_ctas, void* workspace,
+                                               size_t workspace_bytes, float* lse_out, b200attn_stream_t stream) {
+  if (bs == 0) return B200ATTN_OK;
+  DecodeParams p;
+  const int rc = decode_setup(p, out, 8, out, out_tok_stride, out, out, static_cast<int64_t>(Hq) * D, nullptr, 0,
+                              nullptr, nullptr, 0, bs, Hq, Hq, D, q_dtype, q_dtype, 1.f, 0.f, 1.f, 1.f, plan, n_ctas,
+                              workspace, workspace_bytes, lse_out, false);
+  if (rc != B200ATTN_OK) return rc;
+  return launch_merge(p, D, q_dtype == B200ATTN_BF16, static_cast<cudaStream_t>(stream));
 }

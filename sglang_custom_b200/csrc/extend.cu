@@ -1,0 +1,67 @@
+// b200attn_extend: argument checks and the choice between the tcgen05 and the register-MMA kernel.
+// Reference entry points this replaces: TritonAttnBackend.forward_extend
+// (python/sglang/srt/layers/attention/triton_backend.py:632-685) -> extend_attention_fwd
+// (triton_ops/extend_attention.py:306-438); oracle torch_native_backend.py:27-110,182-224.
+#include "extend.cuh"
+
+using namespace b200attn;
+
+extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                                         const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                                         const int32_t* req_to_token, int64_t table_stride,
+                                         const void* req_pool_indices, const void* seq_lens, int idx_is_i64,
+                                         const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+                                         const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq,
+                                         int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale, float logit_cap,
+                                         float k_scale, float v_scale, int causal, int impl, float* lse_out,
+                                         b200attn_stream_t stream) {
+  B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0 && max_extend_len >= 0, B200ATTN_ERR_INVALID,
+             "extend: bad sizes bs=%d Hq=%d Hkv=%d max_extend_len=%d", bs, Hq, Hkv, max_extend_len);
+  if (bs == 0 || max_extend_len == 0) return B200ATTN_OK;
+  B2_REQUIRE(q && out && k_pool && v_pool && req_to_token && req_pool_indices && seq_lens && extend_seq_lens &&
+                 extend_prefix_lens && extend_start_loc,
+             B200ATTN_ERR_INVALID, "extend: null pointer");
+  B2_REQUIRE(Hq % Hkv == 0, B200ATTN_ERR_INVALID, "extend: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
+  B2_REQUIRE(D == 64 || D == 128, B200ATTN_ERR_UNSUPPORTED, "extend: head dim %d (64/128 only)", D);
+  B2_REQUIRE(q_dtype == B200ATTN_BF16 || q_dtype == B200ATTN_F16, B200ATTN_ERR_UNSUPPORTED, "extend: q dtype %d", q_dtype);
+  B2_REQUIRE(kv_dtype == q_dtype || kv_dtype == B200ATTN_FP8_E4M3, B200ATTN_ERR_UNSUPPORTED,
+             "extend: kv dtype %d with q dtype %d", kv_dtype, q_dtype);
+  const int kvb = elem_size(kv_dtype);
+  B2_REQUIRE(aligned16(q) && aligned16(out) && aligned16(k_pool) && aligned16(v_pool) && q_tok_stride % 8 == 0 &&
+                 out_tok_stride % 8 == 0 && (pool_tok_stride * kvb) % 16 == 0,
+             B200ATTN_ERR_INVALID, "extend: tensors must be 16-byte aligned");
+  B2_REQUIRE(pool_tok_stride >= static_cast<int64_t>(Hkv) * D, B200ATTN_ERR_INVALID, "extend: pool_tok_stride < Hkv*D");
+  B2_REQUIRE(k_scale > 0.f && v_scale > 0.f, B200ATTN_ERR_INVALID, "extend: k_scale/v_scale must be > 0");
+  B2_REQUIRE(impl == B200ATTN_EXTEND_AUTO || impl == B200ATTN_EXTEND_TCGEN05 || impl == B200ATTN_EXTEND_MMA,
+             B200ATTN_ERR_INVALID, "extend: impl %d", impl);
+
+  ExtendParams p;
+  p.q = q; p.out = out; p.k_pool = k_pool; p.v_pool = v_pool;
+  p.req_to_token = req_to_token; p.req_pool_indices = req_pool_indices; p.seq_lens = seq_lens;
+  p.extend_seq_lens = extend_seq_lens; p.extend_prefix_lens = extend_prefix_lens;
+  p.extend_start_loc = extend_start_loc;
+  p.lse_out = lse_out;
+  p.q_tok_stride = q_tok_stride; p.out_tok_stride = out_tok_stride;
+  p.pool_tok_stride = pool_tok_stride; p.table_stride = table_stride;
+  p.idx_is_i64 = idx_is_i64;
+  p.bs = bs; p.Hq = Hq; p.Hkv = Hkv; p.G = Hq / Hkv; p.max_extend_len = max_extend_len;
+  p.causal = causal;
+  p.scale_raw = sm_scale * k_scale;
+  p.scale_log2 = sm_scale * k_scale * kLog2e;
+  p.logit_cap = logit_cap;
+  p.v_scale = v_scale;
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool q_bf16 = q_dtype == B200ATTN_BF16;
+  const bool tc_ok = extend_tc_supported(p, D, kvb);
+  if (impl == B200ATTN_EXTEND_TCGEN05) {
+    B2_REQUIRE(tc_ok, B200ATTN_ERR_UNSUPPORTED,
+               "extend: the tcgen05 kernel needs D == 128, 16-bit KV and logit_cap == 0 (D=%d kv bytes=%d cap=%g)", D,
+               kvb, static_cast<double>(logit_cap));
+    return extend_tc_launch(p, q_bf16, st);
+  }
+  // AUTO: dense prefill tiles go to the tensor-memory kernel; short rows (decode rows of a MIXED
+  // batch, tiny chunks) are not worth a 128-row tile.
+  if (impl == B200ATTN_EXTEND_AUTO && tc_ok && max_extend_len >= 128) return extend_tc_launch(p, q_bf16, st);
+  return extend_mma_launch(p, D, kvb, q_bf16, st);
+}

@@ -1,0 +1,36 @@
+// Shared declarations of the extend / prefill kernels.
+#pragma once
+#include "common.cuh"
+
+namespace b200attn {
+
+struct ExtendParams {
+  const void* q;
+  void* out;
+  const void* k_pool;
+  const void* v_pool;
+  const int32_t* req_to_token;
+  const void* req_pool_indices;
+  const void* seq_lens;
+  const int32_t* extend_seq_lens;
+  const int32_t* extend_prefix_lens;
+  const int32_t* extend_start_loc;
+  float* lse_out;  // optional fp32 [T, Hq]
+  int64_t q_tok_stride, out_tok_stride, pool_tok_stride, table_stride;
+  int idx_is_i64;
+  int bs, Hq, Hkv, G, max_extend_len;
+  int causal;
+  float scale_log2;  // sm_scale * k_scale * log2(e)
+  float scale_raw;   // sm_scale * k_scale
+  float logit_cap;
+  float v_scale;
+};
+
+// register-MMA kernel (extend_mma.cu): any shape the library accepts
+int extend_mma_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaStream_t st);
+
+// tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit KV, logit_cap == 0
+bool extend_tc_supported(const ExtendParams& p, int D, int kvb);
+int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st);
+
+}  // namespace b200attn

@@ -99,6 +99,23 @@ def kv_write(k: torch.Tensor, v: torch.Tensor, loc: torch.Tensor, k_pool: torch.
     del keep
 
 
+def set_kv_buffer(k_buffer: torch.Tensor, v_buffer: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
+                  cache_v: torch.Tensor, pool_dtype: torch.dtype, k_scale: ScaleT = None, v_scale: ScaleT = None,
+                  scale_mode: int = _lib.SCALE_DIV, writeback_scaled: bool = False) -> None:
+    """MHATokenToKVPool.set_kv_buffer (memory_pool.py:420-458) on raw layer buffers.
+
+    `k_buffer` is the stored buffer (uint8 for an fp8 pool); `pool_dtype` the logical dtype.
+    As in the reference, scales only apply when a cast happens (cache_k.dtype != pool dtype).
+    scale_mode DIV is torch's CPU `div_` (the oracle); RCP is what torch CUDA does for a python
+    float.  writeback_scaled=True reproduces the reference's in-place `cache_k.div_(k_scale)`."""
+    if loc.dtype != torch.int64:
+        loc = loc.to(torch.int64)
+    if cache_k.dtype == pool_dtype:
+        k_scale = v_scale = None
+    kv_write(cache_k, cache_v, loc.contiguous(), k_buffer, v_buffer, k_scale, v_scale, pool_dtype, scale_mode,
+             writeback_scaled)
+
+
 def decode_plan_bytes(max_bs: int, n_ctas: int) -> int:
     return _lib.load().b200attn_decode_plan_bytes(int(max_bs), int(n_ctas))
 
@@ -120,8 +137,9 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
            plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
            k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
-           lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """q,out [bs,Hq,D]; pools [P,Hkv,D]; see b200attn_decode in include/b200attn.h."""
+           lse_out: Optional[torch.Tensor] = None, stage: str = "both") -> torch.Tensor:
+    """q,out [bs,Hq,D]; pools [P,Hkv,D]; see b200attn_decode in include/b200attn.h.
+    stage: "both" (b200attn_decode), "partial" (stage 1 only) or "merge" (stage 2 only)."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, workspace, lse_out)
     bs, Hq, D = q.shape
     Hkv = k_pool.shape[1]
@@ -137,7 +155,14 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
         raise B200AttnError("decode: pool must be [P,Hkv,D] with strides (*, D, 1)")
     if lse_out is not None and (lse_out.dtype != torch.float32 or not lse_out.is_contiguous()):
         raise B200AttnError("decode: lse_out must be contiguous fp32 [bs,Hq]")
-    check(_lib.load().b200attn_decode(
+    if stage == "merge":
+        check(_lib.load().b200attn_decode_merge(
+            out.data_ptr(), out.stride(0), bs, Hq, D, _dt(q.dtype), plan.data_ptr(), int(n_ctas),
+            workspace.data_ptr(), workspace.numel() * workspace.element_size(), _ptr(lse_out), _stream(q)),
+            "b200attn_decode_merge")
+        return out
+    fn = _lib.load().b200attn_decode if stage == "both" else _lib.load().b200attn_decode_partial
+    check(fn(
         q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
         k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
         seq_lens.data_ptr(), _is_i64(seq_lens), bs, Hq, Hkv, D, _dt(q.dtype), _pool_dtype(k_pool, kv_dtype),
@@ -173,7 +198,7 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            extend_seq_lens: torch.Tensor, extend_prefix_lens: torch.Tensor, extend_start_loc: torch.Tensor,
            max_extend_len: int, sm_scale: float, logit_cap: float = 0.0, k_scale: float = 1.0,
            v_scale: float = 1.0, causal: bool = True, kv_dtype: Optional[torch.dtype] = None,
-           impl: int = _lib.EXTEND_AUTO) -> torch.Tensor:
+           impl: int = _lib.EXTEND_AUTO, lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q,out [T,Hq,D]; see b200attn_extend in include/b200attn.h."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, extend_seq_lens,
           extend_prefix_lens, extend_start_loc)
@@ -198,7 +223,7 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
         seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
         extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
         _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
-        int(bool(causal)), int(impl), _stream(q)), "b200attn_extend")
+        int(bool(causal)), int(impl), _ptr(lse_out), _stream(q)), "b200attn_extend")
     return out
 
 
