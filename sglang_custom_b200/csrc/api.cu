@@ -16,6 +16,7 @@ void set_error(const char* fmt, ...) {
 }
 
 int cuda_fail(cudaError_t e, const char* what) {
+  (void)cudaGetLastError();  // clear the (non-sticky) error so it is not reported again by a later, unrelated call
   set_error("CUDA error %d (%s) in %s", static_cast<int>(e), cudaGetErrorString(e), what);
   return B200ATTN_ERR_CUDA;
 }

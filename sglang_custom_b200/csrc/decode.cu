@@ -565,9 +565,13 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
 // ---------------------------------------------------------------------------------------
 template <int D, int HB, int KVB, bool kQBf16, bool kG8>
 static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
-  // ~192 KiB of staging per SM: 3 stages of 64 KiB (D=128 bf16) or 6 stages of 32/16 KiB
-  constexpr int NSTAGE = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+  // ~192 KiB of staging per SM: 3 stages of 64 KiB (D=128 bf16) or 6 stages of 32/16 KiB; one stage less
+  // when the cross-warp merge buffer cannot alias a stage and the total would pass the 227 KiB CTA limit
+  constexpr int kWant = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+  constexpr int kStatic = 2048;  // static __shared__ (segment list, cursors) + the 1 KiB the driver reserves
+  constexpr int NSTAGE = (DecodeCfg<D, HB, KVB, kWant>::SMEM + kStatic <= 227 * 1024) ? kWant : kWant - 1;
   using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
+  static_assert(Cfg::SMEM + kStatic <= 227 * 1024, "decode staging exceeds the shared memory of one CTA");
   auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE>;
   static bool configured = false;  // per instantiation
   if (!configured) {

@@ -69,11 +69,15 @@ def exact_extend(case, kp, vp, causal: bool = True, logit_cap: float = 0.0, retu
 
 
 def assert_close(got: torch.Tensor, want: torch.Tensor, max_abs: float = MAX_ABS_TOL, mean_abs: float = MEAN_ABS_TOL,
-                 what: str = "") -> None:
+                 what: str = "", rel: bool = False) -> None:
+    """rel=True scales the max-abs bound by max(1, |want|): the output is rounded to bf16 (half an ulp of a value in
+    [2, 4) is already 7.8e-3), which matters only for the tight comparison against the fp64 restatement."""
     g, w = got.detach().float().cpu(), want.detach().float().cpu()
     assert g.shape == w.shape, f"{what}: shape {tuple(g.shape)} vs {tuple(w.shape)}"
     assert torch.isfinite(g).all(), f"{what}: non-finite values in the CUDA output"
     d = (g - w).abs()
+    if rel:
+        d = d / w.abs().clamp(min=1.0)
     mx, mn = float(d.max()) if d.numel() else 0.0, float(d.mean()) if d.numel() else 0.0
     assert mx <= max_abs and mn <= mean_abs, f"{what}: max-abs {mx:.3e} (tol {max_abs}) mean-abs {mn:.3e} (tol {mean_abs})"
 
@@ -102,73 +106,4 @@ def pools_equal(a: torch.Tensor, b: torch.Tensor) -> bool:
 
 
 # ------------------------------------------------------------------ CUDA side
-def to_device(case, device) -> types.SimpleNamespace:
-    d = types.SimpleNamespace(**vars(case))
-    for k, v in vars(case).items():
-        if isinstance(v, torch.Tensor):
-            setattr(d, k, v.to(device))
-    return d
-
-
-class Runner:
-    """Drives the product path exactly as SGLang would: ModelRunner stand-in -> B200AttnBackend ->
-    RadixAttention.forward -> backend.forward_decode / forward_extend -> C ABI."""
-
-    def __init__(self, case, device, max_reqs: Optional[int] = None):
-        from sglang_custom_b200 import interfaces as itf
-        from sglang_custom_b200.backend import B200AttnBackend
-        self.itf = itf
-        self.case = case
-        self.device = device
-        kv_dtype = torch.float8_e4m3fn if case.fp8 else case.dtype
-        cfg = itf.ModelConfig(context_len=case.req_to_token.shape[1], num_attention_heads=case.Hq,
-                              num_key_value_heads=case.Hkv, head_dim=case.D, num_hidden_layers=1)
-        self.mr = itf.ModelRunner(cfg, max_reqs=case.req_to_token.shape[0], pool_size=case.P - case.page_size,
-                                  device=str(device), kv_dtype=kv_dtype, page_size=case.page_size, dtype=case.dtype)
-        self.mr.req_to_token_pool.req_to_token.copy_(case.req_to_token.to(device))
-        pool = self.mr.token_to_kv_pool
-        pool.k_buffer[0].copy_(case.k_pool.to(device))
-        pool.v_buffer[0].copy_(case.v_pool.to(device))
-        self.backend = B200AttnBackend(self.mr)
-        s = case.kv_scale if case.fp8 and case.kv_scale != 1.0 else None
-        self.layer = itf.RadixAttention(num_heads=case.Hq, head_dim=case.D, scaling=case.sm_scale,
-                                        num_kv_heads=case.Hkv, layer_id=0, k_scale_float=s, v_scale_float=s)
-
-    def batch(self, mode=None):
-        itf, c, dev = self.itf, self.case, self.device
-        if mode is None:
-            mode = itf.ForwardMode.DECODE if c.decode else itf.ForwardMode.EXTEND
-        fb = itf.ForwardBatch(
-            forward_mode=mode, batch_size=c.bs, req_pool_indices=c.req_pool_indices.to(dev),
-            seq_lens=c.seq_lens.to(dev), out_cache_loc=c.out_cache_loc.to(dev), seq_lens_sum=c.seq_lens_sum,
-            req_to_token_pool=self.mr.req_to_token_pool, token_to_kv_pool=self.mr.token_to_kv_pool,
-            attn_backend=self.backend, seq_lens_cpu=c.seq_lens.cpu())
-        if not mode.is_decode():
-            fb.extend_seq_lens = c.extend_seq_lens.to(dev)
-            fb.extend_prefix_lens = c.extend_prefix_lens.to(dev)
-            fb.extend_start_loc = c.extend_start_loc.to(dev)
-            fb.extend_seq_lens_cpu = c.extend_seq_lens.tolist()
-            fb.extend_prefix_lens_cpu = c.extend_prefix_lens.tolist()
-            fb.extend_num_tokens = c.T
-        return fb
-
-    def forward(self, mode=None, save_kv_cache: bool = True, strided_qkv: bool = True) -> torch.Tensor:
-        """One attention forward; q/k/v arrive as strided views of one qkv buffer, as in LlamaAttention
-        (models/llama.py:182-193) and as the reference's CPU tests make them on purpose (test_decode.py:105-110)."""
-        c, dev = self.case, self.device
-        fb = self.batch(mode)
-        self.backend.init_forward_metadata(fb)
-        if strided_qkv and c.T > 0:
-            qkv = torch.cat([c.q.reshape(c.T, -1), c.k_new.reshape(c.T, -1), c.v_new.reshape(c.T, -1)], dim=1).to(dev)
-            q, k, v = qkv.split([c.Hq * c.D, c.Hkv * c.D, c.Hkv * c.D], dim=1)
-        else:
-            q = c.q.reshape(c.T, -1).to(dev)
-            k = c.k_new.reshape(c.T, -1).to(dev)
-            v = c.v_new.reshape(c.T, -1).to(dev)
-        out = self.layer.forward(q, k, v, fb, save_kv_cache=save_kv_cache)
-        torch.cuda.synchronize(dev)
-        return out.view(c.T, c.Hq, c.D)
-
-    def pools(self):
-        pool = self.mr.token_to_kv_pool
-        return pool.k_buffer[0], pool.v_buffer[0]
+from sglang_custom_b200.harness import Runner, to_device  # noqa: E402,F401  (oracle-free; bench.py uses it directly)

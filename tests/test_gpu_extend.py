@@ -48,7 +48,7 @@ def test_extend_vs_oracles(bs, Hq, Hkv, D, lens, ext, kw, device):
     dk, dv = r.pools()
     assert H.pools_equal(dk, kp) and H.pools_equal(dv, vp), "KV write must be bit-exact"
     H.assert_close(out, H.oracle_extend(case, kp, vp), what="vs torch_native")
-    H.assert_close(out, H.exact_extend(case, kp, vp), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what="vs fp64 restatement")
+    H.assert_close(out, H.exact_extend(case, kp, vp), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what="vs fp64 restatement", rel=True)
 
 
 def _direct(case, device, kp, vp, impl, causal=True, logit_cap=0.0, want_lse=False):
@@ -71,7 +71,7 @@ def test_both_extend_kernels_agree_with_fp64(impl, lens, ext, device):
     kp, vp = H.pool_after_write(case)
     out, lse = _direct(case, device, kp, vp, impl, want_lse=True)
     want, want_lse = H.exact_extend(case, kp, vp, return_lse=True)
-    H.assert_close(out, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"impl={impl}")
+    H.assert_close(out, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"impl={impl}", rel=True)
     assert torch.allclose(lse.cpu(), want_lse, atol=2e-3, rtol=1e-4)
 
 
@@ -82,14 +82,14 @@ def test_extend_non_causal_encoder_only(impl, device):
     kp, vp = H.pool_after_write(case)
     out = _direct(case, device, kp, vp, impl, causal=False)
     H.assert_close(out, H.oracle_extend(case, kp, vp, causal=False), what="non-causal vs torch_native")
-    H.assert_close(out, H.exact_extend(case, kp, vp, causal=False), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL)
+    H.assert_close(out, H.exact_extend(case, kp, vp, causal=False), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, rel=True)
 
 
 def test_extend_logit_cap(device):
     case = synth.make_case(2, 8, 2, 128, [300, 77], extend_lens=[150, 77], seed=10)
     kp, vp = H.pool_after_write(case)
     out = _direct(case, device, kp, vp, _lib.EXTEND_AUTO, logit_cap=30.0)
-    H.assert_close(out, H.exact_extend(case, kp, vp, logit_cap=30.0), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL)
+    H.assert_close(out, H.exact_extend(case, kp, vp, logit_cap=30.0), H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, rel=True)
 
 
 def test_mixed_batch_equals_decode_for_single_token_rows(device):
@@ -153,4 +153,4 @@ def test_extend_full_size_c3_sampled_oracle(device):
             want_rows.append(H.exact_decode(one, sub.k_pool, sub.v_pool))
         want = torch.cat(want_rows)
         got = out[sub.token_rows[rows].to(device)].cpu()
-        H.assert_close(got, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"C3 request {req}")
+        H.assert_close(got, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"C3 request {req}", rel=True)

@@ -65,7 +65,7 @@ def test_bf16_scatter_whole_pool_bit_exact(dtype, Hkv, D, T, strided, device):
         qkv = torch.cat([c.q.reshape(T, -1), c.k_new.reshape(T, -1), c.v_new.reshape(T, -1)], 1).to(device)
         _, k, v = qkv.split([c.Hq * D, Hkv * D, Hkv * D], dim=1)
         k, v = k.view(T, Hkv, D), v.view(T, Hkv, D)
-        assert not k.is_contiguous()
+        assert T == 1 or not k.is_contiguous()
     else:
         k, v = c.k_new.to(device), c.v_new.to(device)
     ops.set_kv_buffer(dk, dv, c.out_cache_loc.to(device), k, v, dtype)
