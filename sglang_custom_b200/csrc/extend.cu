@@ -2,6 +2,8 @@
 // Reference entry points this replaces: TritonAttnBackend.forward_extend
 // (python/sglang/srt/layers/attention/triton_backend.py:632-685) -> extend_attention_fwd
 // (triton_ops/extend_attention.py:306-438); oracle torch_native_backend.py:27-110,182-224.
+#include <stdlib.h>
+
 #include "extend.cuh"
 
 using namespace b200attn;
@@ -50,6 +52,12 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   p.scale_log2 = sm_scale * k_scale * kLog2e;
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
+  {
+    static const int dbg = [] { const char* e = getenv("B200ATTN_DEBUG"); return e ? atoi(e) : 0; }();
+    p.debug = dbg;
+    static unsigned long long* const prof = [] { const char* e = getenv("B200ATTN_PROF_PTR"); return e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0)) : nullptr; }();
+    p.prof = prof;
+  }
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool q_bf16 = q_dtype == B200ATTN_BF16;

@@ -24,6 +24,8 @@ struct ExtendParams {
   float scale_raw;   // sm_scale * k_scale
   float logit_cap;
   float v_scale;
+  unsigned long long* prof;  // B200ATTN_PROF_PTR: device buffer for clock64 phase timings of CTA (0,0,0) (dev only)
+  int debug;  // B200ATTN_DEBUG bit flags (timing experiments only; results are wrong when set)
 };
 
 // register-MMA kernel (extend_mma.cu): any shape the library accepts

@@ -14,23 +14,28 @@
 //     tcgen05.mma (both operands from 128B-swizzled shared memory); P (bf16) is written back over the first 64
 //     columns of S and O += P V runs in TS mode (A from tensor memory, V as an MN-major B operand), so P never
 //     touches shared memory.
-//   * K/V tiles of 128 tokens are gathered row by row through req_to_token with TMA gather4
-//     (cp.async.bulk.tensor.2d.tile::gather4: four pool rows x 128 bytes per instruction, written in the UMMA
-//     canonical 128B-swizzle layout, completion counted on an mbarrier) -- no flattened kv_indices copy and
-//     no register staging.  Two K and two V buffers of 32 KiB form the ring.
-//   * warp roles: warps 0-3 / 4-7 = softmax + output of Q tile 0 / 1 (one query row per thread, fp32 online
-//     softmax in the log2 domain, the O rescale is lazy: only when the row maximum grows by more than 2^8),
-//     warp 8 = MMA issuer (one thread), warp 9 = TMA producer.  All hand-offs are mbarriers; tcgen05.commit
-//     tracks MMA completion.  Every wait is bounded (ptx::mbar_wait traps instead of hanging).
-#include <cuda.h>  // CUtensorMap and its enums only; the driver entry point is fetched through the runtime
-
+//   * K/V tiles of 128 tokens are gathered row by row through req_to_token by three producer warps with 16-byte
+//     cp.async (LDGSTS) straight into the UMMA canonical 128B-swizzle layout; completion is counted on an
+//     mbarrier with cp.async.mbarrier.arrive.noinc, so the producers never wait for their own copies -- no
+//     flattened kv_indices copy and no register staging.  Two K and two V buffers of 32 KiB form the ring.
+//     (The first cut used TMA gather4, four rows x 128 B per instruction: measured 63 cycles per instruction,
+//     i.e. 8 000 cycles per 128-key K+V tile against a 2 048-cycle MMA budget -- profiles/README.md -- so the
+//     page_size = 1 gather moved to LDGSTS; tma_gather4 stays in tc_ptx.cuh for the paged-tile path.)
+//   * warp roles (three warpgroups, registers re-balanced with setmaxnreg): warps 0-3 / 4-7 = softmax + output
+//     of Q tile 0 / 1 (one query row per thread, fp32 online softmax in the log2 domain on packed f32x2 FMAs, the
+//     O rescale is lazy: only when the row maximum grows by more than 2^8), warp 8 = MMA issuer (one thread),
+//     warps 9-11 = producers.  All hand-offs are mbarriers; tcgen05.commit tracks MMA completion.  Every wait
+//     is bounded (ptx::mbar_wait traps instead of hanging).
 #include "extend.cuh"
 #include "tc_ptx.cuh"
 
 namespace b200attn {
 namespace tc {
 
-constexpr int kThreads = 320;
+constexpr int kThreads = 384;       // 3 warpgroups
+constexpr int kProducerWarps = 3;
+constexpr int kRegsSoftmax = 208;   // setmaxnreg targets: 2 x 128 x 208 + 128 x 80 <= 64 Ki registers
+constexpr int kRegsOther = 80;
 constexpr int kTile = 128;           // BM = BN = D = 128
 constexpr int kTileBytes = 32768;    // 128 rows x 256 B
 constexpr int kHalfBytes = 16384;    // 128 rows x 128 B (one 64-element swizzle atom column)
@@ -43,10 +48,20 @@ constexpr float kRescaleThreshold = 8.0f;                 // log2 units
 
 enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 3, V_FULL = 5, V_EMPTY = 7, S_FULL = 9, P_FULL = 11, O_FULL = 13 };
 
+// dev-only phase timing: CTA (0,0,0) accumulates clock64 deltas into p.prof[slot]
+#define TC_PROF_BEGIN() long long prof_t0 = prof_on ? clock64() : 0
+#define TC_PROF_MARK(slot)                                                          \
+  do {                                                                              \
+    if (prof_on) {                                                                  \
+      const long long now__ = clock64();                                            \
+      prof_acc[slot] += static_cast<unsigned long long>(now__ - prof_t0);           \
+      prof_t0 = now__;                                                              \
+    }                                                                               \
+  } while (0)
+
 template <bool kBf16>
 __global__ void __launch_bounds__(kThreads, 1)
-extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_k,
-                 const __grid_constant__ CUtensorMap tmap_v, const int pair_heads) {
+extend_tc_kernel(const ExtendParams p, const int pair_heads) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms repeat every 1024 B
   const uint32_t bars = smem + kOffBar;
@@ -54,6 +69,8 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
   const uint32_t tmem_slot = bars + 16 * 8;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool prof_on = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  unsigned long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int req = blockIdx.y;
   const int E = p.extend_seq_lens[req];
   const int zt = static_cast<int>(gridDim.z) - 1 - static_cast<int>(blockIdx.z);  // heavy (late) tiles first
@@ -84,19 +101,15 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
   if (tid == 0) {
     ptx::mbar_init(bar(Q_FULL), 256);
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(bar(K_FULL + i), 1);
+      ptx::mbar_init(bar(K_FULL + i), kProducerWarps * 32);
       ptx::mbar_init(bar(K_EMPTY + i), 1);
-      ptx::mbar_init(bar(V_FULL + i), 1);
+      ptx::mbar_init(bar(V_FULL + i), kProducerWarps * 32);
       ptx::mbar_init(bar(V_EMPTY + i), 1);
       ptx::mbar_init(bar(S_FULL + i), 1);
       ptx::mbar_init(bar(P_FULL + i), 128);
       ptx::mbar_init(bar(O_FULL + i), 1);
     }
     ptx::fence_mbar_init();
-  }
-  if (warp == 9 && lane == 0) {
-    ptx::prefetch_tmap(&tmap_k);
-    ptx::prefetch_tmap(&tmap_v);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -105,6 +118,7 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
   asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
 
   if (warp < 8) {
+    ptx::setmaxnreg_inc<kRegsSoftmax>();
     // ================================================================ softmax + output of Q tile t
     const int t = warp >> 2;
     const int wq = warp & 3;          // tensor-memory lane quarter of this warp
@@ -142,16 +156,21 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
       float m_used = 0.f, l = 0.f;
       const int my_n = nt[t];
 
+      TC_PROF_BEGIN();
       for (int j = 0; j < my_n; ++j) {
         ptx::mbar_wait(bar(S_FULL + t), j & 1);
         ptx::tc_fence_after();
+        TC_PROF_MARK(0);
         uint32_t s[4][32];
 #pragma unroll
         for (int c = 0; c < 4; ++c) ptx::tmem_ld32(tS + c * 32, s[c]);
         ptx::tmem_wait_ld();
+        TC_PROF_MARK(1);
 
         const int kv0 = j * kTile;
-        float mx = -INFINITY;
+        float mx8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mx8[i] = -INFINITY;
         if (kv0 + kTile > lim_row0) {  // diagonal or last tile: mask (warp-uniform branch)
           const int nvis = lim - kv0;
 #pragma unroll
@@ -161,15 +180,18 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
               float x = __uint_as_float(s[c][i]);
               x = (c * 32 + i < nvis) ? x : -INFINITY;
               s[c][i] = __float_as_uint(x);
-              mx = fmaxf(mx, x);
+              mx8[i & 7] = fmaxf(mx8[i & 7], x);
             }
         } else {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+            for (int i = 0; i < 32; ++i) mx8[i & 7] = fmaxf(mx8[i & 7], __uint_as_float(s[c][i]));
         }
+        float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
+                         fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
         mx *= p.scale_log2;  // scale > 0: the maximum commutes with the scaling
+        TC_PROF_MARK(2);
 
         if (j == 0) {
           m_used = (mx == -INFINITY) ? 0.f : mx;
@@ -195,30 +217,35 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
           }
         }
 
-        float sum = 0.f;
-        const float neg_m = -m_used;
+        TC_PROF_MARK(3);
+        const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(-m_used, -m_used);
+        float2 sum2[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t pk[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int c = h * 2 + (i >> 4), e = (i & 15) * 2;
-            const float a = fast_exp2(fmaf(__uint_as_float(s[c][e]), p.scale_log2, neg_m));
-            const float b = fast_exp2(fmaf(__uint_as_float(s[c][e + 1]), p.scale_log2, neg_m));
-            sum += a + b;
-            pk[i] = pack2<kBf16>(a, b);
+            float2 x = ptx::ffma2(make_float2(__uint_as_float(s[c][e]), __uint_as_float(s[c][e + 1])), sc2, nm2);
+            if (!(p.debug & 2)) { x.x = fast_exp2(x.x); x.y = fast_exp2(x.y); }
+            sum2[i & 3] = ptx::fadd2(sum2[i & 3], x);
+            pk[i] = pack2<kBf16>(x.x, x.y);
           }
           ptx::tmem_st32(tS + h * 32, pk);
         }
+        const float2 st = ptx::fadd2(ptx::fadd2(sum2[0], sum2[1]), ptx::fadd2(sum2[2], sum2[3]));
+        const float sum = st.x + st.y;
         ptx::tmem_wait_st();
         l += sum;
         ptx::tc_fence_before();
         ptx::mbar_arrive(bar(P_FULL + t));
+        TC_PROF_MARK(4);
       }
 
       // ---- epilogue: O_t / l -> global
       ptx::mbar_wait(bar(O_FULL + t), 0);
       ptx::tc_fence_after();
+      TC_PROF_MARK(5);
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
       uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) +
                       static_cast<int64_t>(start + q0[t] + row) * p.out_tok_stride + static_cast<int64_t>(head[t]) * kTile;
@@ -242,9 +269,13 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
       if (p.lse_out != nullptr && row_valid)
         p.lse_out[static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] =
             l > 0.f ? (m_used + log2f(l)) * kLn2 : -INFINITY;
+      TC_PROF_MARK(6);
+      if (prof_on && lane == 0)
+        for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
       ptx::tc_fence_before();
     }
   } else if (warp == 8) {
+    ptx::setmaxnreg_dec<kRegsOther>();
     // ================================================================ MMA issuer (one thread)
     if (lane == 0) {
       constexpr int kFmt = kBf16 ? 1 : 0;
@@ -278,9 +309,12 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
         }
       };
 
+      TC_PROF_BEGIN();
       ptx::mbar_wait(bar(Q_FULL), 0);
       ptx::mbar_wait(bar(K_FULL + 0), 0);
+      ptx::fence_proxy_async();  // K/V arrive through cp.async (generic proxy); the tensor core reads through the async proxy
       ptx::tc_fence_after();
+      TC_PROF_MARK(0);
       for (int t = 0; t < 2; ++t)
         if (nt[t] > 0) issue_qk(t, 0);
       ptx::umma_commit(bar(K_EMPTY + 0));
@@ -290,14 +324,21 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
         bool v_ready = false, k_ready = false;
         for (int t = 0; t < 2; ++t) {
           if (j < nt[t]) {
+            TC_PROF_MARK(7);
             ptx::mbar_wait(bar(P_FULL + t), j & 1);
+            TC_PROF_MARK(1 + t);
             if (!v_ready) { ptx::mbar_wait(bar(V_FULL + vb), (j >> 1) & 1); v_ready = true; }
+            TC_PROF_MARK(3);
+            ptx::fence_proxy_async();
             ptx::tc_fence_after();
             issue_pv(t, vb, j > 0);
             if (j == nt[t] - 1) ptx::umma_commit(bar(O_FULL + t));
           }
           if (j + 1 < nt[t]) {
+            TC_PROF_MARK(7);
             if (!k_ready) { ptx::mbar_wait(bar(K_FULL + kb), ((j + 1) >> 1) & 1); k_ready = true; }
+            TC_PROF_MARK(4);
+            ptx::fence_proxy_async();
             ptx::tc_fence_after();
             issue_qk(t, kb);
           }
@@ -305,37 +346,71 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
         ptx::umma_commit(bar(V_EMPTY + vb));
         if (j + 1 < n) ptx::umma_commit(bar(K_EMPTY + kb));
       }
+      TC_PROF_MARK(7);
+      if (prof_on)
+        for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
     }
   } else {
-    // ================================================================ TMA producer: gather K/V rows through the page table
+    ptx::setmaxnreg_dec<kRegsOther>();
+    // ================================================================ producers: gather K/V rows through the page table
+    // A warp instruction copies two pool rows of this kv head (2 x 256 B, 16 lanes x 16 B each); row pair i of a
+    // tile goes to producer warp i % 3.  Each lane reads the slots of its own rows straight from the page table
+    // (a broadcast load per half warp), once per tile, and uses them for both the K and the V gather.
+    const int pw = warp - 9;
     const int32_t* trow = p.req_to_token + load_index(p.req_pool_indices, p.idx_is_i64, req) * p.table_stride;
-    const int col = kv_head * kTile;
+    const int64_t row_bytes = p.pool_tok_stride * 2;
+    const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+    const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+    const int sub = lane >> 4;                       // which row of the pair
+    const int ch = lane & 15;                        // 16-byte chunk of the 256-byte row
+    constexpr int kPairsPerWarp = (64 + kProducerWarps - 1) / kProducerWarps;  // 22
+    // slots of the rows this lane copies: row r_k = 2 * (pw + 3 k) + sub  (16 lanes share an address: broadcast).
+    // The slots of tile j + 1 are fetched before the gathers of tile j are issued, so the index load never queues
+    // behind this warp's own copies.
+    int slot[kPairsPerWarp], slot_next[kPairsPerWarp];
+    auto load_slots = [&](int j, int (&dst)[kPairsPerWarp]) {
+#pragma unroll
+      for (int k = 0; k < kPairsPerWarp; ++k) {
+        const int r = 2 * (pw + kProducerWarps * k) + sub;
+        const int tok = j * kTile + r;
+        dst[k] = (r < kTile && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
+      }
+    };
+    load_slots(0, slot_next);
+    TC_PROF_BEGIN();
     for (int j = 0; j < n; ++j) {
       const int b = j & 1, u = j >> 1;
-      int idx[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int tok = j * kTile + 4 * lane + i;
-        idx[i] = tok < kv_len ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked in the softmax)
-      }
-      const uint32_t row_off = static_cast<uint32_t>(4 * lane) * 128u;
+      for (int k = 0; k < kPairsPerWarp; ++k) slot[k] = slot_next[k];
+      if (j + 1 < n) load_slots(j + 1, slot_next);
+      TC_PROF_MARK(0);
+      auto gather = [&](const uint8_t* base, uint32_t tile) {
+#pragma unroll
+        for (int k = 0; k < kPairsPerWarp; ++k) {
+          const int r = 2 * (pw + kProducerWarps * k) + sub;
+          if (2 * (pw + kProducerWarps * k) < kTile) {  // warp-uniform
+            const uint32_t dst = tile + (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
+            cp_async16(dst, base + static_cast<int64_t>(slot[k]) * row_bytes);
+          }
+        }
+      };
       // K_j
       ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
-      if (lane == 0) ptx::mbar_arrive_expect_tx(bar(K_FULL + b), kTileBytes);
-      __syncwarp();
-#pragma unroll
-      for (int h = 0; h < 2; ++h)
-        ptx::tma_gather4(smem + kOffK + b * kTileBytes + h * kHalfBytes + row_off, &tmap_k, col + h * 64, idx[0],
-                         idx[1], idx[2], idx[3], bar(K_FULL + b));
+      TC_PROF_MARK(1);
+      if (!(p.debug & 1)) gather(kbase, smem + kOffK + b * kTileBytes);
+      TC_PROF_MARK(2);
+      ptx::cp_async_mbar_arrive_noinc(bar(K_FULL + b));
+      TC_PROF_MARK(5);
       // V_j
       ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
-      if (lane == 0) ptx::mbar_arrive_expect_tx(bar(V_FULL + b), kTileBytes);
-      __syncwarp();
-#pragma unroll
-      for (int h = 0; h < 2; ++h)
-        ptx::tma_gather4(smem + kOffV + b * kTileBytes + h * kHalfBytes + row_off, &tmap_v, col + h * 64, idx[0],
-                         idx[1], idx[2], idx[3], bar(V_FULL + b));
+      TC_PROF_MARK(3);
+      if (!(p.debug & 1)) gather(vbase, smem + kOffV + b * kTileBytes);
+      TC_PROF_MARK(4);
+      ptx::cp_async_mbar_arrive_noinc(bar(V_FULL + b));
+      TC_PROF_MARK(6);
     }
+    if (prof_on && lane == 0)
+      for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
   }
 
   // ---------------------------------------------------------------- teardown
@@ -347,40 +422,6 @@ extend_tc_kernel(const ExtendParams p, const __grid_constant__ CUtensorMap tmap_
   }
 }
 
-// ---------------------------------------------------------------- host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (fn == nullptr) {
-    void* sym = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(sym);
-  }
-  return fn;
-}
-
-// pool [rows, pool_tok_stride] of 16-bit elements; box = 64 elements x 1 row (gather4 loads four such rows)
-static int make_pool_tmap(CUtensorMap* map, const void* pool, int64_t pool_tok_stride, int row_elems, bool bf16) {
-  EncodeTiledFn fn = encode_fn();
-  B2_REQUIRE(fn != nullptr, B200ATTN_ERR_CUDA, "extend: cuTensorMapEncodeTiled is not available from this driver");
-  const cuuint64_t dims[2] = {static_cast<cuuint64_t>(row_elems), static_cast<cuuint64_t>(1) << 31};
-  const cuuint64_t strides[1] = {static_cast<cuuint64_t>(pool_tok_stride) * 2};
-  const cuuint32_t box[2] = {64, 1};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult rc = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
-                         const_cast<void*>(pool), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  B2_REQUIRE(rc == CUDA_SUCCESS, B200ATTN_ERR_CUDA, "extend: cuTensorMapEncodeTiled failed with CUresult %d",
-             static_cast<int>(rc));
-  return B200ATTN_OK;
-}
-
 }  // namespace tc
 
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb) {
@@ -388,13 +429,6 @@ bool extend_tc_supported(const ExtendParams& p, int D, int kvb) {
 }
 
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st) {
-  alignas(64) CUtensorMap tk, tv;
-  const int row_elems = p.Hkv * tc::kTile;
-  int rc = tc::make_pool_tmap(&tk, p.k_pool, p.pool_tok_stride, row_elems, q_bf16);
-  if (rc != B200ATTN_OK) return rc;
-  rc = tc::make_pool_tmap(&tv, p.v_pool, p.pool_tok_stride, row_elems, q_bf16);
-  if (rc != B200ATTN_OK) return rc;
-
   auto kern = q_bf16 ? tc::extend_tc_kernel<true> : tc::extend_tc_kernel<false>;
   static bool configured[2] = {false, false};
   if (!configured[q_bf16]) {
@@ -406,7 +440,7 @@ int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st) {
   dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.bs, pair_heads ? q_tiles : (q_tiles + 1) / 2);
   B2_REQUIRE(grid.y <= 65535 && grid.z <= 65535, B200ATTN_ERR_UNSUPPORTED, "extend: batch %d or %d q tiles exceed the grid",
              p.bs, q_tiles);
-  kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, tk, tv, pair_heads);
+  kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, pair_heads);
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
 }
