@@ -53,8 +53,11 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
   {
-    static const int dbg = [] { const char* e = getenv("B200ATTN_DEBUG"); return e ? atoi(e) : 0; }();
-    p.debug = dbg;
+    // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
+    static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 2; }();
+    p.exp_emu = emu;
+    static const int order = [] { const char* e = getenv("B200ATTN_GRID_ORDER"); return e ? atoi(e) : 0; }();
+    p.grid_order = order;
     static unsigned long long* const prof = [] { const char* e = getenv("B200ATTN_PROF_PTR"); return e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0)) : nullptr; }();
     p.prof = prof;
   }

@@ -13,7 +13,13 @@
 //   * tensor memory (512 columns): S0 | S1 | O0 | O1, 128 fp32 columns each.  S = Q K^T is an SS-mode
 //     tcgen05.mma (both operands from 128B-swizzled shared memory); P (bf16) is written back over the first 64
 //     columns of S and O += P V runs in TS mode (A from tensor memory, V as an MN-major B operand), so P never
-//     touches shared memory.
+//     touches shared memory.  P is handed over in two 64-key halves, so the first four PV k-steps start while
+//     the softmax warps still work on the second half.
+//   * exp2 is the co-limit: 2 x 128 x 128 exponentials per K/V tile are 2048 MUFU cycles per SM at 16/clk -- as
+//     long as the 2048 tensor cycles of the four MMAs.  kEmu of every four element pairs are therefore computed
+//     on the FMA pipe instead (ptx::exp2_poly2: Cody-Waite split + degree-3 minimax polynomial on packed f32x2,
+//     7.5e-5 relative error, invisible after the bf16 rounding of P); masked (diagonal / last) tiles use MUFU only
+//     so that masked keys are exact zeros.
 //   * K/V tiles of 128 tokens are gathered row by row through req_to_token by three producer warps with 16-byte
 //     cp.async (LDGSTS) straight into the UMMA canonical 128B-swizzle layout; completion is counted on an
 //     mbarrier with cp.async.mbarrier.arrive.noinc, so the producers never wait for their own copies -- no
@@ -23,9 +29,12 @@
 //     page_size = 1 gather moved to LDGSTS; tma_gather4 stays in tc_ptx.cuh for the paged-tile path.)
 //   * warp roles (three warpgroups, registers re-balanced with setmaxnreg): warps 0-3 / 4-7 = softmax + output
 //     of Q tile 0 / 1 (one query row per thread, fp32 online softmax in the log2 domain on packed f32x2 FMAs, the
-//     O rescale is lazy: only when the row maximum grows by more than 2^8), warp 8 = MMA issuer (one thread),
-//     warps 9-11 = producers.  All hand-offs are mbarriers; tcgen05.commit tracks MMA completion.  Every wait
-//     is bounded (ptx::mbar_wait traps instead of hanging).
+//     O rescale is lazy: only when the row maximum grows by more than 2^8), warp 8 = MMA issuer (the whole warp
+//     stays converged so descriptors live in uniform registers; one elected lane issues), warps 9-11 = producers.
+//     All hand-offs are mbarriers; tcgen05.commit tracks MMA completion.  Every wait is bounded (ptx::mbar_wait
+//     traps instead of hanging).
+//   * grid order: head pair fastest, then q tile (heavy first), then request -- the CTAs in flight at any time
+//     stream the K/V of one request, which therefore stays in L2 across its 16 head pairs x q tiles.
 #include "extend.cuh"
 #include "tc_ptx.cuh"
 
@@ -34,8 +43,10 @@ namespace tc {
 
 constexpr int kThreads = 384;       // 3 warpgroups
 constexpr int kProducerWarps = 3;
-constexpr int kRegsSoftmax = 208;   // setmaxnreg targets: 2 x 128 x 208 + 128 x 80 <= 64 Ki registers
-constexpr int kRegsOther = 80;
+// setmaxnreg targets.  The CTA is launched with 168 registers per thread (64 512 in its pool), so the 128 threads of the
+// third warpgroup must release at least what the 256 softmax threads claim: 128 x (168 - 88) = 256 x (208 - 168).
+constexpr int kRegsSoftmax = 208;
+constexpr int kRegsOther = 88;
 constexpr int kTile = 128;           // BM = BN = D = 128
 constexpr int kTileBytes = 32768;    // 128 rows x 256 B
 constexpr int kHalfBytes = 16384;    // 128 rows x 128 B (one 64-element swizzle atom column)
@@ -43,37 +54,141 @@ constexpr int kOffQ = 0;             // Q0, Q1
 constexpr int kOffK = 2 * kTileBytes;
 constexpr int kOffV = 4 * kTileBytes;
 constexpr int kOffBar = 6 * kTileBytes;
-constexpr int kSmemBytes = kOffBar + 16 * 8 + 16 + 1024;  // + barriers + tmem slot + alignment slack
+constexpr int kSmemBytes = kOffBar + 32 * 8 + 16 + 1024;  // + barriers + tmem slot + alignment slack
 constexpr float kRescaleThreshold = 8.0f;                 // log2 units
 
-enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 3, V_FULL = 5, V_EMPTY = 7, S_FULL = 9, P_FULL = 11, O_FULL = 13 };
+// P_FULL + 2 * t + h: half h (64 keys) of P_t is in tensor memory
+enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 3, V_FULL = 5, V_EMPTY = 7, S_FULL = 9, O_FULL = 11, P_FULL = 13, kNumBars = 17 };
 
-// dev-only phase timing: CTA (0,0,0) accumulates clock64 deltas into p.prof[slot]
-#define TC_PROF_BEGIN() long long prof_t0 = prof_on ? clock64() : 0
-#define TC_PROF_MARK(slot)                                                          \
-  do {                                                                              \
-    if (prof_on) {                                                                  \
-      const long long now__ = clock64();                                            \
-      prof_acc[slot] += static_cast<unsigned long long>(now__ - prof_t0);           \
-      prof_t0 = now__;                                                              \
-    }                                                                               \
-  } while (0)
+// dev-only phase timing (kernel variant kProf): every warp accumulates clock64 deltas, CTA (0,0,0) stores them
+template <bool kOn>
+struct Prof {
+  unsigned long long acc[8];
+  long long t0;
+  __device__ __forceinline__ void begin() {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0;
+    t0 = clock64();
+  }
+  __device__ __forceinline__ void mark(int slot) {
+    const long long now = clock64();
+    acc[slot] += static_cast<unsigned long long>(now - t0);
+    t0 = now;
+  }
+  __device__ __forceinline__ void flush(unsigned long long* dst, int warp, int lane) {
+    if (dst != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+      for (int i = 0; i < 8; ++i) dst[warp * 8 + i] = acc[i];
+  }
+};
+template <>
+struct Prof<false> {
+  __device__ __forceinline__ void begin() {}
+  __device__ __forceinline__ void mark(int) {}
+  __device__ __forceinline__ void flush(unsigned long long*, int, int) {}
+};
 
-template <bool kBf16>
+// One K/V tile of one query row: S (fp32, tensor memory) -> online-softmax update -> P (bf16, tensor memory).
+//   kMask: some of the 128 keys are invisible to some row (diagonal / last tile) -> mask, MUFU only
+//   kEmu : of every 4 element pairs, kEmu take the FMA-pipe exp2
+template <bool kBf16, bool kMask, int kEmu, bool kProf>
+__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const uint32_t bar_s,
+                                             const uint32_t bar_p, const int j, const int nvis,
+                                             const float scale_log2, float& m_used, float& l, Prof<kProf>& prof) {
+  ptx::mbar_wait(bar_s, j & 1);
+  ptx::tc_fence_after();
+  prof.mark(0);
+  uint32_t s[128];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) ptx::tmem_ld32(tS + c * 32, s + 32 * c);
+  ptx::tmem_wait_ld();
+  prof.mark(1);
+
+  if constexpr (kMask) {
+#pragma unroll
+    for (int i = 0; i < 128; ++i) s[i] = (i < nvis) ? s[i] : 0xff800000u;  // -inf
+  }
+  float mx8[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) mx8[i] = fmaxf(__uint_as_float(s[i]), __uint_as_float(s[8 + i]));
+#pragma unroll
+  for (int i = 16; i < 128; i += 16)
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      mx8[k] = fmaxf(fmaxf(mx8[k], __uint_as_float(s[i + k])), __uint_as_float(s[i + 8 + k]));
+  float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
+                   fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
+  mx *= scale_log2;  // scale > 0: the maximum commutes with the scaling
+  prof.mark(2);
+
+  if (j == 0) {
+    m_used = (mx == -INFINITY) ? 0.f : mx;
+  } else {
+    const bool grow = mx > m_used + kRescaleThreshold;
+    if (__any_sync(0xffffffffu, grow)) {
+      // S_t(j) is complete, so PV_t(j-1) -- issued before it -- is complete too: O_t is stable until this
+      // thread group hands P_t(j) to the MMA warp
+      const float m_new = grow ? mx : m_used;
+      const float f = fast_exp2(m_used - m_new);
+      l *= f;
+      m_used = m_new;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        ptx::tmem_ld32(tO + c * 32, o);
+        ptx::tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+        ptx::tmem_st32(tO + c * 32, o);
+      }
+      ptx::tmem_wait_st();
+    }
+  }
+  prof.mark(3);
+
+  const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_used, -m_used);
+  float2 sum2[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t pk[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const int e = h * 64 + 2 * i;
+      float2 x = ptx::ffma2(make_float2(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), sc2, nm2);
+      if (!kMask && (i & 3) < kEmu) {
+        x = ptx::exp2_poly2(x);
+      } else {
+        x.x = fast_exp2(x.x);
+        x.y = fast_exp2(x.y);
+      }
+      sum2[i & 3] = ptx::fadd2(sum2[i & 3], x);
+      pk[i] = pack2<kBf16>(x.x, x.y);
+    }
+    ptx::tmem_st32(tS + h * 32, pk);
+    ptx::tmem_wait_st();
+    ptx::tc_fence_before();
+    ptx::mbar_arrive(bar_p + 8u * h);
+  }
+  const float2 st = ptx::fadd2(ptx::fadd2(sum2[0], sum2[1]), ptx::fadd2(sum2[2], sum2[3]));
+  l += st.x + st.y;
+  prof.mark(4);
+}
+
+template <bool kBf16, int kEmu, bool kProf>
 __global__ void __launch_bounds__(kThreads, 1)
 extend_tc_kernel(const ExtendParams p, const int pair_heads) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms repeat every 1024 B
   const uint32_t bars = smem + kOffBar;
   auto bar = [&](int i) { return bars + 8u * static_cast<uint32_t>(i); };
-  const uint32_t tmem_slot = bars + 16 * 8;
+  const uint32_t tmem_slot = bars + 32 * 8;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool prof_on = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
-  unsigned long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const int req = blockIdx.y;
+  Prof<kProf> prof;
+  const int req = p.grid_order ? blockIdx.z : blockIdx.y;
   const int E = p.extend_seq_lens[req];
-  const int zt = static_cast<int>(gridDim.z) - 1 - static_cast<int>(blockIdx.z);  // heavy (late) tiles first
+  // heavy (late) tiles first
+  const int zt = p.grid_order ? static_cast<int>(gridDim.y) - 1 - static_cast<int>(blockIdx.y)
+                              : static_cast<int>(gridDim.z) - 1 - static_cast<int>(blockIdx.z);
   int head[2], q0[2];
   if (pair_heads) {
     head[0] = 2 * blockIdx.x; head[1] = head[0] + 1;
@@ -106,8 +221,9 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
       ptx::mbar_init(bar(V_FULL + i), kProducerWarps * 32);
       ptx::mbar_init(bar(V_EMPTY + i), 1);
       ptx::mbar_init(bar(S_FULL + i), 1);
-      ptx::mbar_init(bar(P_FULL + i), 128);
       ptx::mbar_init(bar(O_FULL + i), 1);
+      ptx::mbar_init(bar(P_FULL + 2 * i), 128);
+      ptx::mbar_init(bar(P_FULL + 2 * i + 1), 128);
     }
     ptx::fence_mbar_init();
   }
@@ -155,97 +271,22 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
       const int lim_row0 = p.causal ? min(P + q0[t] + 1, L) : L;                     // the tile's smallest limit
       float m_used = 0.f, l = 0.f;
       const int my_n = nt[t];
+      const int n_unmasked = min(my_n, lim_row0 / kTile);  // tiles every row of this Q tile sees completely
+      const uint32_t bar_s = bar(S_FULL + t), bar_p = bar(P_FULL + 2 * t);
 
-      TC_PROF_BEGIN();
-      for (int j = 0; j < my_n; ++j) {
-        ptx::mbar_wait(bar(S_FULL + t), j & 1);
-        ptx::tc_fence_after();
-        TC_PROF_MARK(0);
-        uint32_t s[4][32];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) ptx::tmem_ld32(tS + c * 32, s[c]);
-        ptx::tmem_wait_ld();
-        TC_PROF_MARK(1);
-
-        const int kv0 = j * kTile;
-        float mx8[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) mx8[i] = -INFINITY;
-        if (kv0 + kTile > lim_row0) {  // diagonal or last tile: mask (warp-uniform branch)
-          const int nvis = lim - kv0;
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              float x = __uint_as_float(s[c][i]);
-              x = (c * 32 + i < nvis) ? x : -INFINITY;
-              s[c][i] = __float_as_uint(x);
-              mx8[i & 7] = fmaxf(mx8[i & 7], x);
-            }
-        } else {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx8[i & 7] = fmaxf(mx8[i & 7], __uint_as_float(s[c][i]));
-        }
-        float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
-                         fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
-        mx *= p.scale_log2;  // scale > 0: the maximum commutes with the scaling
-        TC_PROF_MARK(2);
-
-        if (j == 0) {
-          m_used = (mx == -INFINITY) ? 0.f : mx;
-        } else {
-          const bool grow = mx > m_used + kRescaleThreshold;
-          if (__any_sync(0xffffffffu, grow)) {
-            // S_t(j) is complete, so PV_t(j-1) -- issued before it -- is complete too: O_t is stable until this
-            // thread group hands P_t(j) to the MMA warp
-            const float m_new = grow ? mx : m_used;
-            const float f = fast_exp2(m_used - m_new);
-            l *= f;
-            m_used = m_new;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              uint32_t o[32];
-              ptx::tmem_ld32(tO + c * 32, o);
-              ptx::tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-              ptx::tmem_st32(tO + c * 32, o);
-            }
-            ptx::tmem_wait_st();
-          }
-        }
-
-        TC_PROF_MARK(3);
-        const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(-m_used, -m_used);
-        float2 sum2[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t pk[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int c = h * 2 + (i >> 4), e = (i & 15) * 2;
-            float2 x = ptx::ffma2(make_float2(__uint_as_float(s[c][e]), __uint_as_float(s[c][e + 1])), sc2, nm2);
-            if (!(p.debug & 2)) { x.x = fast_exp2(x.x); x.y = fast_exp2(x.y); }
-            sum2[i & 3] = ptx::fadd2(sum2[i & 3], x);
-            pk[i] = pack2<kBf16>(x.x, x.y);
-          }
-          ptx::tmem_st32(tS + h * 32, pk);
-        }
-        const float2 st = ptx::fadd2(ptx::fadd2(sum2[0], sum2[1]), ptx::fadd2(sum2[2], sum2[3]));
-        const float sum = st.x + st.y;
-        ptx::tmem_wait_st();
-        l += sum;
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(bar(P_FULL + t));
-        TC_PROF_MARK(4);
-      }
+      prof.begin();
+      int j = 0;
+#pragma unroll 1
+      for (; j < n_unmasked; ++j)
+        softmax_tile<kBf16, false, kEmu, kProf>(tS, tO, bar_s, bar_p, j, kTile, p.scale_log2, m_used, l, prof);
+#pragma unroll 1
+      for (; j < my_n; ++j)
+        softmax_tile<kBf16, true, kEmu, kProf>(tS, tO, bar_s, bar_p, j, lim - j * kTile, p.scale_log2, m_used, l, prof);
 
       // ---- epilogue: O_t / l -> global
       ptx::mbar_wait(bar(O_FULL + t), 0);
       ptx::tc_fence_after();
-      TC_PROF_MARK(5);
+      prof.mark(5);
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
       uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) +
                       static_cast<int64_t>(start + q0[t] + row) * p.out_tok_stride + static_cast<int64_t>(head[t]) * kTile;
@@ -269,93 +310,119 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
       if (p.lse_out != nullptr && row_valid)
         p.lse_out[static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] =
             l > 0.f ? (m_used + log2f(l)) * kLn2 : -INFINITY;
-      TC_PROF_MARK(6);
-      if (prof_on && lane == 0)
-        for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
+      prof.mark(6);
+      prof.flush(p.prof, warp, lane);
       ptx::tc_fence_before();
     }
   } else if (warp == 8) {
     ptx::setmaxnreg_dec<kRegsOther>();
-    // ================================================================ MMA issuer (one thread)
-    if (lane == 0) {
-      constexpr int kFmt = kBf16 ? 1 : 0;
-      constexpr uint32_t idesc_qk = ptx::instr_desc_f16(kFmt, 128, 128, 0);  // A = Q, B = K: both K-major
-      constexpr uint32_t idesc_pv = ptx::instr_desc_f16(kFmt, 128, 128, 1);  // A = P (tmem), B = V: MN-major
-      const uint32_t tS[2] = {tmem_base, tmem_base + 128};
-      const uint32_t tO[2] = {tmem_base + 256, tmem_base + 384};
-      // K-major SW128: 8-row groups 1024 B apart; a 16-element k step is 32 B inside the 128 B atom row,
-      // the second 64-element half of D lives in the next 16 KiB sub-tile
-      auto desc_k_major = [&](uint32_t tile) { return ptx::smem_desc_sw128(tile, 16, 1024); };
-      // MN-major SW128 (V: rows = keys = the contraction index, 128 B of D per row): 8-key groups 1024 B apart
-      // (SBO), the two 64-element halves of D 16 KiB apart (LBO); a 16-key k step is 2048 B
-      auto desc_mn_major = [&](uint32_t tile) { return ptx::smem_desc_sw128(tile, kHalfBytes, 1024); };
-      const uint64_t qd[2] = {desc_k_major(smem + kOffQ), desc_k_major(smem + kOffQ + kTileBytes)};
-      const uint64_t kd[2] = {desc_k_major(smem + kOffK), desc_k_major(smem + kOffK + kTileBytes)};
-      const uint64_t vd[2] = {desc_mn_major(smem + kOffV), desc_mn_major(smem + kOffV + kTileBytes)};
+    // ================================================================ MMA issuer
+    // The whole warp walks the loop (mbarrier waits included) so that every operand stays warp-uniform; one
+    // elected lane -- the same one throughout, tcgen05.commit tracks the MMAs of the issuing thread -- issues.
+    const bool leader = ptx::elect_one();
+    constexpr int kFmt = kBf16 ? 1 : 0;
+    constexpr uint32_t idesc_qk = ptx::instr_desc_f16(kFmt, 128, 128, 0);  // A = Q, B = K: both K-major
+    constexpr uint32_t idesc_pv = ptx::instr_desc_f16(kFmt, 128, 128, 1);  // A = P (tmem), B = V: MN-major
+    // K-major SW128: 8-row groups 1024 B apart; a 16-element k step is 32 B inside the 128 B atom row,
+    // the second 64-element half of D lives in the next 16 KiB sub-tile.
+    // MN-major SW128 (V: rows = keys = the contraction index, 128 B of D per row): 8-key groups 1024 B apart
+    // (SBO), the two 64-element halves of D 16 KiB apart (LBO); a 16-key k step is 2048 B.
+    const uint64_t qd0 = ptx::smem_desc_sw128(smem + kOffQ, 16, 1024);
+    const uint64_t kd0 = ptx::smem_desc_sw128(smem + kOffK, 16, 1024);
+    const uint64_t vd0 = ptx::smem_desc_sw128(smem + kOffV, kHalfBytes, 1024);
+    constexpr uint64_t kTileStep = kTileBytes >> 4;  // descriptor address units of 16 B
 
-      auto issue_qk = [&](int t, int kb) {
+    auto issue_qk = [&](int t, int kb) {
+      const uint64_t qd = qd0 + static_cast<uint64_t>(t) * kTileStep;
+      const uint64_t kd = kd0 + static_cast<uint64_t>(kb) * kTileStep;
+      const uint32_t d = tmem_base + t * 128;
+      if (leader) {
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t off = static_cast<uint64_t>(((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4);
-          ptx::umma_ss(tS[t], qd[t] + off, kd[kb] + off, idesc_qk, kk > 0 ? 1u : 0u);
+          ptx::umma_ss(d, qd + off, kd + off, idesc_qk, kk > 0 ? 1u : 0u);
         }
         ptx::umma_commit(bar(S_FULL + t));
-      };
-      auto issue_pv = [&](int t, int vb, bool acc) {
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const uint64_t off = static_cast<uint64_t>((kk * 2048) >> 4);
-          ptx::umma_ts(tO[t], tS[t] + kk * 8, vd[vb] + off, idesc_pv, (acc || kk > 0) ? 1u : 0u);
-        }
-      };
-
-      TC_PROF_BEGIN();
-      ptx::mbar_wait(bar(Q_FULL), 0);
-      ptx::mbar_wait(bar(K_FULL + 0), 0);
-      ptx::fence_proxy_async();  // K/V arrive through cp.async (generic proxy); the tensor core reads through the async proxy
-      ptx::tc_fence_after();
-      TC_PROF_MARK(0);
-      for (int t = 0; t < 2; ++t)
-        if (nt[t] > 0) issue_qk(t, 0);
-      ptx::umma_commit(bar(K_EMPTY + 0));
-
-      for (int j = 0; j < n; ++j) {
-        const int vb = j & 1, kb = (j + 1) & 1;
-        bool v_ready = false, k_ready = false;
-        for (int t = 0; t < 2; ++t) {
-          if (j < nt[t]) {
-            TC_PROF_MARK(7);
-            ptx::mbar_wait(bar(P_FULL + t), j & 1);
-            TC_PROF_MARK(1 + t);
-            if (!v_ready) { ptx::mbar_wait(bar(V_FULL + vb), (j >> 1) & 1); v_ready = true; }
-            TC_PROF_MARK(3);
-            ptx::fence_proxy_async();
-            ptx::tc_fence_after();
-            issue_pv(t, vb, j > 0);
-            if (j == nt[t] - 1) ptx::umma_commit(bar(O_FULL + t));
-          }
-          if (j + 1 < nt[t]) {
-            TC_PROF_MARK(7);
-            if (!k_ready) { ptx::mbar_wait(bar(K_FULL + kb), ((j + 1) >> 1) & 1); k_ready = true; }
-            TC_PROF_MARK(4);
-            ptx::fence_proxy_async();
-            ptx::tc_fence_after();
-            issue_qk(t, kb);
-          }
-        }
-        ptx::umma_commit(bar(V_EMPTY + vb));
-        if (j + 1 < n) ptx::umma_commit(bar(K_EMPTY + kb));
       }
-      TC_PROF_MARK(7);
-      if (prof_on)
-        for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
+      __syncwarp();
+    };
+    // four k-steps (64 keys) of O_t += P_t V
+    auto issue_pv_half = [&](int t, int vb, int h, bool acc) {
+      const uint64_t vd = vd0 + static_cast<uint64_t>(vb) * kTileStep + static_cast<uint64_t>(h) * ((4 * 2048) >> 4);
+      const uint32_t d = tmem_base + 256 + t * 128;
+      const uint32_t a = tmem_base + t * 128 + h * 32;
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          ptx::umma_ts(d, a + kk * 8, vd + static_cast<uint64_t>((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
+      }
+      __syncwarp();
+    };
+    auto commit = [&](int b) {
+      if (leader) ptx::umma_commit(bar(b));
+      __syncwarp();
+    };
+
+    prof.begin();
+    ptx::mbar_wait(bar(Q_FULL), 0);
+    ptx::mbar_wait(bar(K_FULL + 0), 0);
+    ptx::fence_proxy_async();  // K/V arrive through cp.async (generic proxy); the tensor core reads through the async proxy
+    ptx::tc_fence_after();
+    prof.mark(0);
+    for (int t = 0; t < 2; ++t)
+      if (nt[t] > 0) issue_qk(t, 0);
+    commit(K_EMPTY + 0);
+    prof.mark(7);
+
+#pragma unroll 1
+    for (int j = 0; j < n; ++j) {
+      const int vb = j & 1, kb = (j + 1) & 1;
+      bool v_ready = false, k_ready = false;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (j < nt[t]) {
+          ptx::mbar_wait(bar(P_FULL + 2 * t), j & 1);
+          prof.mark(1 + t);
+          if (!v_ready) {
+            ptx::mbar_wait(bar(V_FULL + vb), (j >> 1) & 1);
+            ptx::fence_proxy_async();
+            v_ready = true;
+            prof.mark(3);
+          }
+          ptx::tc_fence_after();
+          issue_pv_half(t, vb, 0, j > 0);
+          prof.mark(7);
+          ptx::mbar_wait(bar(P_FULL + 2 * t + 1), j & 1);
+          prof.mark(5);
+          ptx::tc_fence_after();
+          issue_pv_half(t, vb, 1, true);
+          if (j == nt[t] - 1) commit(O_FULL + t);
+          prof.mark(7);
+        }
+        if (j + 1 < nt[t]) {
+          if (!k_ready) {
+            ptx::mbar_wait(bar(K_FULL + kb), ((j + 1) >> 1) & 1);
+            ptx::fence_proxy_async();
+            k_ready = true;
+            prof.mark(4);
+          }
+          ptx::tc_fence_after();
+          issue_qk(t, kb);
+          prof.mark(7);
+        }
+      }
+      commit(V_EMPTY + vb);
+      if (j + 1 < n) commit(K_EMPTY + kb);
+      prof.mark(7);
     }
+    prof.flush(p.prof, warp, lane);
   } else {
     ptx::setmaxnreg_dec<kRegsOther>();
     // ================================================================ producers: gather K/V rows through the page table
-    // A warp instruction copies two pool rows of this kv head (2 x 256 B, 16 lanes x 16 B each); row pair i of a
-    // tile goes to producer warp i % 3.  Each lane reads the slots of its own rows straight from the page table
-    // (a broadcast load per half warp), once per tile, and uses them for both the K and the V gather.
+    // A warp instruction copies two pool rows of this kv head (2 x 256 B, 16 lanes x 16 B each).  The 128 rows of a
+    // tile are 16 groups of 8 (one swizzle period); producer warp pw owns groups m = pw, pw + 3, ... and walks a
+    // group as four row pairs q, so the swizzled destination of (group k', pair q) is base_q + k' * 3072: four
+    // loop-invariant registers instead of one per copy.
     const int pw = warp - 9;
     const int32_t* trow = p.req_to_token + load_index(p.req_pool_indices, p.idx_is_i64, req) * p.table_stride;
     const int64_t row_bytes = p.pool_tok_stride * 2;
@@ -363,54 +430,63 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
     const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
     const int sub = lane >> 4;                       // which row of the pair
     const int ch = lane & 15;                        // 16-byte chunk of the 256-byte row
-    constexpr int kPairsPerWarp = (64 + kProducerWarps - 1) / kProducerWarps;  // 22
-    // slots of the rows this lane copies: row r_k = 2 * (pw + 3 k) + sub  (16 lanes share an address: broadcast).
-    // The slots of tile j + 1 are fetched before the gathers of tile j are issued, so the index load never queues
-    // behind this warp's own copies.
-    int slot[kPairsPerWarp], slot_next[kPairsPerWarp];
-    auto load_slots = [&](int j, int (&dst)[kPairsPerWarp]) {
+    constexpr int kGroups = 6;                       // groups per producer warp (the last one only for pw == 0)
+    uint32_t dst_q[4];                               // destination of (group pw, pair q) relative to the tile base
 #pragma unroll
-      for (int k = 0; k < kPairsPerWarp; ++k) {
-        const int r = 2 * (pw + kProducerWarps * k) + sub;
-        const int tok = j * kTile + r;
-        dst[k] = (r < kTile && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
+    for (int q = 0; q < 4; ++q) {
+      const int r = 8 * pw + 2 * q + sub;
+      dst_q[q] = (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
+    }
+    // Page-table slots: lane i of load c holds the slot of row 8 * (pw + 3 * (4 c + i / 8)) + i % 8 -- the rows of
+    // this warp only, two coalesced-by-eight loads per tile, fetched one tile ahead; the copy of (group k', pair q)
+    // takes its slot from lane 8 * (k' % 4) + 2 q + sub of register k' / 4 with a shuffle.
+    int sreg[2];
+    auto load_slots = [&](int j) {
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int m = pw + 3 * (4 * c + (lane >> 3));
+        const int tok = j * kTile + 8 * m + (lane & 7);
+        sreg[c] = (m < 16 && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
       }
     };
-    load_slots(0, slot_next);
-    TC_PROF_BEGIN();
+    int slot[4 * kGroups];
+    auto spread_slots = [&]() {
+#pragma unroll
+      for (int kq = 0; kq < 4 * kGroups; ++kq) {
+        const int kp = kq >> 2, q = kq & 3;
+        slot[kq] = __shfl_sync(0xffffffffu, sreg[kp >> 2], 8 * (kp & 3) + 2 * q + sub);
+      }
+    };
+    auto gather = [&](const uint8_t* base, uint32_t tile) {
+#pragma unroll
+      for (int kq = 0; kq < 4 * kGroups; ++kq) {
+        const int kp = kq >> 2, q = kq & 3;
+        if (pw + 3 * kp < 16)  // warp-uniform
+          cp_async16(tile + dst_q[q] + kp * 3072, base + static_cast<int64_t>(slot[kq]) * row_bytes);
+      }
+    };
+    load_slots(0);
+    prof.begin();
+#pragma unroll 1
     for (int j = 0; j < n; ++j) {
       const int b = j & 1, u = j >> 1;
-#pragma unroll
-      for (int k = 0; k < kPairsPerWarp; ++k) slot[k] = slot_next[k];
-      if (j + 1 < n) load_slots(j + 1, slot_next);
-      TC_PROF_MARK(0);
-      auto gather = [&](const uint8_t* base, uint32_t tile) {
-#pragma unroll
-        for (int k = 0; k < kPairsPerWarp; ++k) {
-          const int r = 2 * (pw + kProducerWarps * k) + sub;
-          if (2 * (pw + kProducerWarps * k) < kTile) {  // warp-uniform
-            const uint32_t dst = tile + (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
-            cp_async16(dst, base + static_cast<int64_t>(slot[k]) * row_bytes);
-          }
-        }
-      };
+      spread_slots();
+      if (j + 1 < n) load_slots(j + 1);  // issued before this tile's copies so that it never queues behind them
+      prof.mark(0);
       // K_j
       ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
-      TC_PROF_MARK(1);
-      if (!(p.debug & 1)) gather(kbase, smem + kOffK + b * kTileBytes);
-      TC_PROF_MARK(2);
+      prof.mark(1);
+      gather(kbase, smem + kOffK + b * kTileBytes);
       ptx::cp_async_mbar_arrive_noinc(bar(K_FULL + b));
-      TC_PROF_MARK(5);
+      prof.mark(2);
       // V_j
       ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
-      TC_PROF_MARK(3);
-      if (!(p.debug & 1)) gather(vbase, smem + kOffV + b * kTileBytes);
-      TC_PROF_MARK(4);
+      prof.mark(3);
+      gather(vbase, smem + kOffV + b * kTileBytes);
       ptx::cp_async_mbar_arrive_noinc(bar(V_FULL + b));
-      TC_PROF_MARK(6);
+      prof.mark(4);
     }
-    if (prof_on && lane == 0)
-      for (int i = 0; i < 8; ++i) p.prof[warp * 8 + i] = prof_acc[i];
+    prof.flush(p.prof, warp, lane);
   }
 
   // ---------------------------------------------------------------- teardown
@@ -428,16 +504,30 @@ bool extend_tc_supported(const ExtendParams& p, int D, int kvb) {
   return D == 128 && kvb == 2 && p.logit_cap == 0.f && p.Hq >= 1 && (p.pool_tok_stride * 2) % 16 == 0;
 }
 
-int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st) {
-  auto kern = q_bf16 ? tc::extend_tc_kernel<true> : tc::extend_tc_kernel<false>;
-  static bool configured[2] = {false, false};
-  if (!configured[q_bf16]) {
-    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes));
-    configured[q_bf16] = true;
+namespace {
+using KernelFn = void (*)(const ExtendParams, const int);
+
+template <bool kBf16>
+KernelFn pick_kernel(int emu, bool prof) {
+  if (prof) return tc::extend_tc_kernel<kBf16, 2, true>;
+  switch (emu) {
+    case 0: return tc::extend_tc_kernel<kBf16, 0, false>;
+    case 1: return tc::extend_tc_kernel<kBf16, 1, false>;
+    case 3: return tc::extend_tc_kernel<kBf16, 3, false>;
+    default: return tc::extend_tc_kernel<kBf16, 2, false>;
   }
+}
+}  // namespace
+
+int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st) {
+  const int emu = (p.exp_emu >= 0 && p.exp_emu <= 3) ? p.exp_emu : 2;
+  KernelFn kern = q_bf16 ? pick_kernel<true>(emu, p.prof != nullptr) : pick_kernel<false>(emu, p.prof != nullptr);
+  // opt in to the large dynamic shared memory once per kernel instance (cheap host call, no device sync)
+  B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes));
   const int pair_heads = (p.G % 2 == 0) ? 1 : 0;
   const int q_tiles = (p.max_extend_len + tc::kTile - 1) / tc::kTile;
-  dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.bs, pair_heads ? q_tiles : (q_tiles + 1) / 2);
+  const int nz = pair_heads ? q_tiles : (q_tiles + 1) / 2;
+  dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.grid_order ? nz : p.bs, p.grid_order ? p.bs : nz);
   B2_REQUIRE(grid.y <= 65535 && grid.z <= 65535, B200ATTN_ERR_UNSUPPORTED, "extend: batch %d or %d q tiles exceed the grid",
              p.bs, q_tiles);
   kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, pair_heads);

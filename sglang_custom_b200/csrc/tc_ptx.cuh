@@ -34,7 +34,7 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    if (++spins > (1u << 20)) __trap();  // ~4 s of try_wait time-outs
   }
 }
 
@@ -79,6 +79,52 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   return d;
 }
 
+__device__ __forceinline__ float2 fsub2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n"
+      ".reg .b64 ra, rb, rd;\n"
+      "mov.b64 ra, {%2, %3};\n"
+      "mov.b64 rb, {%4, %5};\n"
+      "sub.rn.f32x2 rd, ra, rb;\n"
+      "mov.b64 {%0, %1}, rd;\n"
+      "}\n"
+      : "=f"(d.x), "=f"(d.y)
+      : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+
+// 2^x for a pair on the FMA pipe (no MUFU): round-to-nearest split x = n + r, r in [-0.5, 0.5], degree-3 minimax
+// polynomial for 2^r (max relative error 7.5e-5, far below the bf16 rounding P receives), exponent patched in with an
+// integer add.  x is clamped at -125 (results below 2^-125 flush to 2^-125 ~ 2.4e-38 instead of 0).
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -125.f);
+  x.y = fmaxf(x.y, -125.f);
+  const float2 magic = make_float2(12582912.f, 12582912.f);  // 1.5 * 2^23: the low mantissa bits of x + magic hold round(x)
+  const float2 t = fadd2(x, magic);
+  const float2 n = fsub2(t, magic);
+  const float2 r = fsub2(x, n);
+  float2 p = ffma2(r, make_float2(0.0551716685295105f, 0.0551716685295105f), make_float2(0.2426111251115799f, 0.2426111251115799f));
+  p = ffma2(p, r, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  p = ffma2(p, r, make_float2(0.9999280571937561f, 0.9999280571937561f));
+  float2 y;
+  y.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(t.x) << 23));
+  y.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(t.y) << 23));
+  return y;
+}
+
+// one lane of a converged warp (the same lane every time): the issuer of tcgen05.mma / tcgen05.commit
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ------------------------------------------------------------------ fences
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
@@ -109,7 +155,7 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {  // the warp that
 }
 
 // 32 lanes x 32 columns of 32-bit: thread i of the warp gets lane (quarter base + i), columns [c, c+32)
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -121,7 +167,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "r"(taddr)
       : "memory");
 }
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* v) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
       "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
