@@ -68,6 +68,48 @@ __global__ void k(float* out, long long* cyc, float a, float b) {
       } else if (OP == 13) {  // FMUL2 pair, pair
         asm volatile("{.reg .b64 ra, rb; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3};"
                      "mul.rn.f32x2 ra, ra, rb; mov.b64 {%0, %1}, ra;}" : "+f"(x[i]), "+f"(x[i + 1]) : "f"(y[i]), "f"(y[i + 1]));
+      } else if (OP == 15) {  // MUFU.EX2 bf16x2 (1 per pair)
+        uint32_t r = __float_as_uint(x[i]);
+        asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(r));
+        x[i] = __uint_as_float(r);
+      } else if (OP == 16) {  // MUFU.EX2 f16x2 (1 per pair)
+        uint32_t r = __float_as_uint(x[i]);
+        asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(r));
+        x[i] = __uint_as_float(r);
+      } else if (OP == 17) {  // mix: FFMA2(imm) + F2FP
+        asm volatile("{.reg .b64 ra, rb, rc; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3}; mov.b64 rc, {0f3F000000, 0f3F000000};"
+                     "fma.rn.f32x2 ra, ra, rb, rc; mov.b64 {%0, %1}, ra;}" : "+f"(x[i]), "+f"(x[i + 1]) : "f"(y[i]), "f"(y[i + 1]));
+        uint32_t r;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(y[i]), "f"(y[i + 1]));
+        y[i] = __uint_as_float(r);
+      } else if (OP == 18) {  // mix: 2 FMNMX + F2FP
+        asm volatile("max.f32 %0, %0, %1;" : "+f"(x[i]) : "f"(y[i + 1]));
+        asm volatile("max.f32 %0, %0, %1;" : "+f"(x[i + 1]) : "f"(y[i]));
+        uint32_t r;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(y[i]), "f"(y[i + 1]));
+        y[i] = __uint_as_float(r);
+      } else if (OP == 19) {  // the emu-0 softmax mix per pair: FFMA2 + 2 MUFU + FADD2 + F2FP + FMNMX3
+        asm volatile("{.reg .b64 ra, rb, rc; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3}; mov.b64 rc, {0fBF000000, 0fBF000000};"
+                     "fma.rn.f32x2 ra, ra, rb, rc; mov.b64 {%0, %1}, ra;}" : "+f"(x[i]), "+f"(x[i + 1]) : "f"(y[i]), "f"(y[i + 1]));
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[i]));
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[i + 1]));
+        asm volatile("{.reg .b64 ra, rb; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3};"
+                     "add.rn.f32x2 ra, ra, rb; mov.b64 {%0, %1}, ra;}" : "+f"(y[i]), "+f"(y[i + 1]) : "f"(x[i]), "f"(x[i + 1]));
+        uint32_t r;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(x[i]), "f"(x[i + 1]));
+        asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(y[i]) : "f"(x[i]), "f"(__uint_as_float(r)));
+      } else if (OP == 20) {  // bf16x2-MUFU softmax mix per pair: FFMA2 + F2FP + MUFU.bf16x2 + 2 unpack + FADD2 + FMNMX3
+        asm volatile("{.reg .b64 ra, rb, rc; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3}; mov.b64 rc, {0fBF000000, 0fBF000000};"
+                     "fma.rn.f32x2 ra, ra, rb, rc; mov.b64 {%0, %1}, ra;}" : "+f"(x[i]), "+f"(x[i + 1]) : "f"(y[i]), "f"(y[i + 1]));
+        uint32_t r;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(x[i + 1]), "f"(x[i]));
+        asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(r));
+        float lo, hi;
+        asm volatile("shl.b32 %0, %1, 16;" : "=f"(lo) : "r"(r));
+        asm volatile("and.b32 %0, %1, 0xffff0000;" : "=f"(hi) : "r"(r));
+        asm volatile("{.reg .b64 ra, rb; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3};"
+                     "add.rn.f32x2 ra, ra, rb; mov.b64 {%0, %1}, ra;}" : "+f"(y[i]), "+f"(y[i + 1]) : "f"(lo), "f"(hi));
+        asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(x[i]) : "f"(lo), "f"(hi));
       } else if (OP == 14) {  // FADD reg, reg x2
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(x[i]) : "f"(y[i]));
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(x[i + 1]) : "f"(y[i + 1]));
@@ -113,6 +155,12 @@ int main() {
   run<7>("FMNMX", 2);
   run<8>("F2FP.BF16.PACK", 1);
   run<11>("IMAD shl-add", 2);
+  run<15>("MUFU.EX2 bf16x2", 1);
+  run<16>("MUFU.EX2 f16x2", 1);
+  run<17>("mix FFMA2(imm) + F2FP", 2);
+  run<18>("mix 2 FMNMX + F2FP", 3);
+  run<19>("softmax mix emu0 (6 instr/pair)", 6);
+  run<20>("softmax mix bf16x2 MUFU (7/pair)", 7);
   run<10>("mix 2 MUFU + 1 FFMA2(imm)", 3);
   run<12>("mix 1 FFMA2(imm) + 2 FMNMX", 3);
   cudaError_t e = cudaDeviceSynchronize();

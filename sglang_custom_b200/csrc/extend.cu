@@ -54,9 +54,9 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   p.v_scale = v_scale;
   {
     // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
-    static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 2; }();
+    static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 0; }();
     p.exp_emu = emu;
-    static const int order = [] { const char* e = getenv("B200ATTN_GRID_ORDER"); return e ? atoi(e) : 0; }();
+    static const int order = [] { const char* e = getenv("B200ATTN_GRID_ORDER"); return e ? atoi(e) : 1; }();
     p.grid_order = order;
     static unsigned long long* const prof = [] { const char* e = getenv("B200ATTN_PROF_PTR"); return e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0)) : nullptr; }();
     p.prof = prof;

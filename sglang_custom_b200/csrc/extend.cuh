@@ -26,7 +26,7 @@ struct ExtendParams {
   float v_scale;
   unsigned long long* prof;  // B200ATTN_PROF_PTR: device buffer for clock64 phase timings of CTA (0,0,0) (dev only)
   int grid_order;  // tcgen05 kernel: 0 = (head pair, request, q tile), 1 = (head pair, q tile, request)  (B200ATTN_GRID_ORDER)
-  int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 2)
+  int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 0: measured best at C3)
 };
 
 // register-MMA kernel (extend_mma.cu): any shape the library accepts
