@@ -163,18 +163,33 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
 
     auto seg_tiles = [&](int s) { return (segs[s].tok_end - segs[s].tok_begin + NT - 1) / NT; };
 
-    // stage the token slots of one tile into the index ring (first NT threads)
-    auto stage_indices = [&]() {
+    // Token slots of one tile -> index ring (first NT threads), in two steps so that the page-table load is never
+    // waited for: fetch_indices() issues the load into a register, store_indices() -- one tile step later, just
+    // before the barrier that publishes the ring -- writes it to shared memory.  (The first cut stored right
+    // after the load: the STS stalled on the full global-load latency every step, 19 % of all stall samples in
+    // profiles/r01_decode_fp8_full.)
+    int32_t pend_slot = -1;
+    int pend_pos = -1;
+    auto fetch_indices = [&]() {
       if (p_idx_seg >= n_segs) return;
       if (tid < NT) {
         const Segment& s = segs[p_idx_seg];
         const int tok = s.tok_begin + p_idx_tile * NT + tid;
-        int32_t slot = -1;
-        if (tok < s.tok_end) slot = __ldg(p.req_to_token + s.table_off + tok);
-        idx_ring[(p_idx_count % (NSTAGE + 1)) * NT + tid] = slot;
+        pend_slot = (tok < s.tok_end) ? __ldg(p.req_to_token + s.table_off + tok) : -1;
+        pend_pos = (p_idx_count % (NSTAGE + 1)) * NT + tid;
       }
       ++p_idx_count;
       if (++p_idx_tile >= seg_tiles(p_idx_seg)) { p_idx_tile = 0; ++p_idx_seg; }
+    };
+    auto store_indices = [&]() {
+      if (pend_pos >= 0) {
+        idx_ring[pend_pos] = pend_slot;
+        pend_pos = -1;
+      }
+    };
+    auto stage_indices = [&]() {  // prologue: fetch + store at once
+      fetch_indices();
+      store_indices();
     };
 
     // issue the gathers of one tile (all threads); always commits a group
@@ -264,9 +279,10 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
 
       for (int t = 0; t < ntiles; ++t) {
         cp_async_wait<NSTAGE - 2>();
+        store_indices();   // slots fetched during the previous step (made visible by the barrier)
         __syncthreads();
         issue_tile();      // refills the stage consumed in the previous iteration
-        stage_indices();   // indices for the tile after that (made visible by the next barrier)
+        fetch_indices();   // page-table load for the tile after that; lands while this step computes
 
         const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
         const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
