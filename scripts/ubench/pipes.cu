@@ -110,6 +110,33 @@ __global__ void k(float* out, long long* cyc, float a, float b) {
         asm volatile("{.reg .b64 ra, rb; mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3};"
                      "add.rn.f32x2 ra, ra, rb; mov.b64 {%0, %1}, ra;}" : "+f"(y[i]), "+f"(y[i + 1]) : "f"(lo), "f"(hi));
         asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(x[i]) : "f"(lo), "f"(hi));
+      } else if (OP == 21) {  // F2FP e4m3x2 -> f16x2, x2
+        uint32_t r0 = __float_as_uint(x[i]), r1 = __float_as_uint(x[i + 1]);
+        asm volatile("{.reg .b16 lo, hi; mov.b32 {lo, hi}, %0; cvt.rn.f16x2.e4m3x2 %0, lo;}" : "+r"(r0));
+        asm volatile("{.reg .b16 lo, hi; mov.b32 {lo, hi}, %0; cvt.rn.f16x2.e4m3x2 %0, lo;}" : "+r"(r1));
+        x[i] = __uint_as_float(r0); x[i + 1] = __uint_as_float(r1);
+      } else if (OP == 22) {  // PRMT x2
+        uint32_t r0 = __float_as_uint(x[i]), r1 = __float_as_uint(x[i + 1]);
+        asm volatile("prmt.b32 %0, %0, %1, 0x1404;" : "+r"(r0) : "r"(__float_as_uint(y[i])));
+        asm volatile("prmt.b32 %0, %0, %1, 0x3424;" : "+r"(r1) : "r"(__float_as_uint(y[i + 1])));
+        x[i] = __uint_as_float(r0); x[i + 1] = __uint_as_float(r1);
+      } else if (OP == 23) {  // LOP3 x2
+        uint32_t r0 = __float_as_uint(x[i]), r1 = __float_as_uint(x[i + 1]);
+        asm volatile("lop3.b32 %0, %0, %1, 0x80808080, 0xE4;" : "+r"(r0) : "r"(__float_as_uint(y[i])));
+        asm volatile("lop3.b32 %0, %0, %1, 0x80808080, 0xE4;" : "+r"(r1) : "r"(__float_as_uint(y[i + 1])));
+        x[i] = __uint_as_float(r0); x[i + 1] = __uint_as_float(r1);
+      } else if (OP == 24) {  // mix: 2 MUFU + 2 F2FP e4m3 unpack (same pipe?)
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[i]));
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[i + 1]));
+        uint32_t r0 = __float_as_uint(y[i]), r1 = __float_as_uint(y[i + 1]);
+        asm volatile("{.reg .b16 lo, hi; mov.b32 {lo, hi}, %0; cvt.rn.f16x2.e4m3x2 %0, lo;}" : "+r"(r0));
+        asm volatile("{.reg .b16 lo, hi; mov.b32 {lo, hi}, %0; cvt.rn.f16x2.e4m3x2 %0, lo;}" : "+r"(r1));
+        y[i] = __uint_as_float(r0); y[i + 1] = __uint_as_float(r1);
+      } else if (OP == 25) {  // SHF x2
+        uint32_t r0 = __float_as_uint(x[i]), r1 = __float_as_uint(x[i + 1]);
+        asm volatile("shr.b32 %0, %0, 1;" : "+r"(r0));
+        asm volatile("shl.b32 %0, %0, 7;" : "+r"(r1));
+        x[i] = __uint_as_float(r0); x[i + 1] = __uint_as_float(r1);
       } else if (OP == 14) {  // FADD reg, reg x2
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(x[i]) : "f"(y[i]));
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(x[i + 1]) : "f"(y[i + 1]));
@@ -161,6 +188,11 @@ int main() {
   run<18>("mix 2 FMNMX + F2FP", 3);
   run<19>("softmax mix emu0 (6 instr/pair)", 6);
   run<20>("softmax mix bf16x2 MUFU (7/pair)", 7);
+  run<21>("F2FP e4m3x2->f16x2", 2);
+  run<22>("PRMT", 2);
+  run<23>("LOP3", 2);
+  run<25>("SHF", 2);
+  run<24>("mix 2 MUFU + 2 F2FP.e4m3", 4);
   run<10>("mix 2 MUFU + 1 FFMA2(imm)", 3);
   run<12>("mix 1 FFMA2(imm) + 2 FMNMX", 3);
   cudaError_t e = cudaDeviceSynchronize();

@@ -67,6 +67,9 @@ class ForwardMetadata:
     seq_lens: Optional[torch.Tensor] = None
     extend_start_loc: Optional[torch.Tensor] = None
     max_extend_len: int = 0
+    # MIXED batches: the running (decode) requests are appended after the prefill requests with
+    # extend_len = 1 (schedule_batch.py:1310-1338); that tail is served by the decode kernel
+    n_decode_tail: int = 0
 
 
 class B200AttnBackend(AttentionBackend):
@@ -106,6 +109,7 @@ class B200AttnBackend(AttentionBackend):
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.scale_mode = _lib.SCALE_DIV
         self.writeback_scaled_kv = False
+        self.route_decode_tail = True  # MIXED batches: extend_len == 1 tail rows go to the decode kernel
 
     # ------------------------------------------------------------------ buffers
     def _alloc_decode_buffers(self, max_bs: int) -> None:
@@ -127,15 +131,25 @@ class B200AttnBackend(AttentionBackend):
             self.forward_metadata = ForwardMetadata(True, bs)
             return
         ext_cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
+        n_tail = 0
         if ext_cpu is not None:
-            max_extend = max(ext_cpu) if len(ext_cpu) else 0
+            ext_cpu = list(ext_cpu)
+            if self.route_decode_tail:
+                while n_tail < len(ext_cpu) and ext_cpu[len(ext_cpu) - 1 - n_tail] == 1:
+                    n_tail += 1
+            head = ext_cpu[:len(ext_cpu) - n_tail]
+            max_extend = max(head) if head else 0
         else:  # the reference's own (syncing) way, triton_backend.py:320
             max_extend = int(forward_batch.extend_seq_lens.max().item()) if bs else 0
         start = getattr(forward_batch, "extend_start_loc", None)
         if start is None and bs:
             ext = forward_batch.extend_seq_lens
             start = (torch.cumsum(ext, 0) - ext).to(torch.int32)
-        self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend)
+        if n_tail:
+            # a query with extend_len 1 at position L-1 sees all L keys: exactly a decode row
+            ops.decode_plan(forward_batch.seq_lens[bs - n_tail:], self.n_ctas, self.plan, self.min_units_per_cta)
+        self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend,
+                                                n_decode_tail=n_tail)
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -232,10 +246,21 @@ class B200AttnBackend(AttentionBackend):
         lid = layer.layer_id - getattr(pool, "start_layer", 0)
         pool.get_key_buffer(layer.layer_id)
         k_scale, v_scale = self._kv_scales(layer)
-        ops.extend(q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
-                   o.view(-1, layer.tp_q_head_num, layer.v_head_dim), pool.k_buffer[lid], pool.v_buffer[lid],
-                   forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
-                   forward_batch.seq_lens, forward_batch.extend_seq_lens, forward_batch.extend_prefix_lens,
-                   md.extend_start_loc, md.max_extend_len, layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0,
-                   k_scale, v_scale, causal=causal, kv_dtype=pool.dtype)
+        q3 = q.view(-1, layer.tp_q_head_num, layer.qk_head_dim)
+        o3 = o.view(-1, layer.tp_q_head_num, layer.v_head_dim)
+        table = forward_batch.req_to_token_pool.req_to_token
+        cap = getattr(layer, "logit_cap", 0.0) or 0.0
+        n_tail = md.n_decode_tail  # a 1-token row sees all L keys with or without the causal mask
+        n_ext = md.bs - n_tail
+        t_ext = q3.shape[0] - n_tail
+        if n_ext > 0 and t_ext > 0:
+            ops.extend(q3[:t_ext], o3[:t_ext], pool.k_buffer[lid], pool.v_buffer[lid], table,
+                       forward_batch.req_pool_indices[:n_ext], forward_batch.seq_lens[:n_ext],
+                       forward_batch.extend_seq_lens[:n_ext], forward_batch.extend_prefix_lens[:n_ext],
+                       md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling, cap, k_scale, v_scale,
+                       causal=causal, kv_dtype=pool.dtype)
+        if n_tail > 0:
+            ops.decode(q3[t_ext:], o3[t_ext:], pool.k_buffer[lid], pool.v_buffer[lid], table,
+                       forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan, self.n_ctas,
+                       self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)
         return o

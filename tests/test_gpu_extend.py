@@ -104,6 +104,35 @@ def test_mixed_batch_equals_decode_for_single_token_rows(device):
     H.assert_close(o_ext, o_dec, 4e-3, 3e-4, what="mixed vs decode")
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(fp8=True, kv_scale=0.1135), dict(page_size=16)])
+def test_mixed_batch_prefill_rows_plus_decode_tail(kw, device):
+    """A real MIXED forward (schedule_batch.py:1310-1338): prefill requests first, the running decode requests
+    appended with extend_len 1.  The backend serves the tail with the decode kernel and the head with the extend
+    kernel; both routes must equal the oracle's single forward_extend."""
+    lens = [384, 200, 1500, 33, 700, 1, 129]
+    ext = [256, 200, 1, 1, 1, 1, 1]
+    case = synth.make_case(len(lens), 16, 4, 128, lens, extend_lens=ext, seed=77, **kw)
+    kp, vp = H.pool_after_write(case)
+    want = H.oracle_extend(case, kp, vp)
+    r = H.Runner(case, device)
+    got = r.forward(r.itf.ForwardMode.MIXED)
+    assert r.backend.forward_metadata.n_decode_tail == 5 and r.backend.forward_metadata.max_extend_len == 256
+    H.assert_close(got, want, what="mixed (decode tail routed)")
+    r2 = H.Runner(case, device)
+    r2.backend.route_decode_tail = False
+    got2 = r2.forward(r2.itf.ForwardMode.MIXED)
+    assert r2.backend.forward_metadata.n_decode_tail == 0
+    H.assert_close(got2, want, what="mixed (all rows through extend)")
+    H.assert_close(got, got2, 8e-3, 6e-4, what="mixed: the two routes")
+    # a batch of only 1-token rows under EXTEND mode: everything goes to the decode kernel
+    case1 = synth.make_case(3, 16, 4, 128, [90, 1, 400], extend_lens=[1, 1, 1], seed=78, **kw)
+    kp, vp = H.pool_after_write(case1)
+    r3 = H.Runner(case1, device)
+    got3 = r3.forward()
+    assert r3.backend.forward_metadata.n_decode_tail == 3
+    H.assert_close(got3, H.oracle_extend(case1, kp, vp), what="all-tail extend")
+
+
 def test_extend_chunked_prefill_equals_one_shot(device):
     """Chunked prefill (scheduler.py:452-457): chunk 2 sees chunk 1 as cached prefix; same result as one extend."""
     L = 700
