@@ -19,12 +19,14 @@ def main():
     bs, P, E, Hq, Hkv, D = 16, 2048, 2048, 32, 8, 128
     if len(sys.argv) > 1:
         bs, P, E = (int(x) for x in sys.argv[1:4])
-    c = synth.make_case_device(bs, Hq, Hkv, D, [P + E] * bs, dev, extend_lens=[E] * bs, seed=1237)
+    fp8 = "fp8" in sys.argv
+    page = 16 if "page16" in sys.argv else 1
+    c = synth.make_case_device(bs, Hq, Hkv, D, [P + E] * bs, dev, extend_lens=[E] * bs, seed=1237, fp8=fp8, page_size=page)
     out = torch.empty_like(c.q)
     fl = synth.algorithmic_extend_flops([E] * bs, [P] * bs, Hq, D)
     fn = lambda: ops.extend(c.q, out, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.seq_lens,
                             c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, E, c.sm_scale,
-                            impl=_lib.EXTEND_TCGEN05)
+                            kv_dtype=torch.float8_e4m3fn if fp8 else None, impl=_lib.EXTEND_TCGEN05)
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
@@ -35,7 +37,7 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
-    print(f"extend bs={bs} P={P} E={E}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
+    print(f"extend bs={bs} P={P} E={E} fp8={fp8} page={page}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
     if prof is not None:
         pr = prof.cpu().view(16, 8)
         n_it = (P + E + 127) // 128

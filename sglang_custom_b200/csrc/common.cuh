@@ -151,5 +151,14 @@ __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint16_t x) {
   return r;
 }
 
+// 16-byte streaming global load (read-only path, no L1 allocation)
+__device__ __forceinline__ uint4 ld_nc_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
 #endif  // __CUDACC__
 }  // namespace b200attn

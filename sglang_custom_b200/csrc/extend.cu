@@ -67,12 +67,12 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   const bool tc_ok = extend_tc_supported(p, D, kvb);
   if (impl == B200ATTN_EXTEND_TCGEN05) {
     B2_REQUIRE(tc_ok, B200ATTN_ERR_UNSUPPORTED,
-               "extend: the tcgen05 kernel needs D == 128, 16-bit KV and logit_cap == 0 (D=%d kv bytes=%d cap=%g)", D,
+               "extend: the tcgen05 kernel needs D == 128 and logit_cap == 0 (D=%d kv bytes=%d cap=%g)", D,
                kvb, static_cast<double>(logit_cap));
-    return extend_tc_launch(p, q_bf16, st);
+    return extend_tc_launch(p, q_bf16, kvb, st);
   }
   // AUTO: dense prefill tiles go to the tensor-memory kernel; short rows (decode rows of a MIXED
   // batch, tiny chunks) are not worth a 128-row tile.
-  if (impl == B200ATTN_EXTEND_AUTO && tc_ok && max_extend_len >= 128) return extend_tc_launch(p, q_bf16, st);
+  if (impl == B200ATTN_EXTEND_AUTO && tc_ok && max_extend_len >= 128) return extend_tc_launch(p, q_bf16, kvb, st);
   return extend_mma_launch(p, D, kvb, q_bf16, st);
 }

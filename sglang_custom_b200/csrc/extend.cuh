@@ -32,8 +32,8 @@ struct ExtendParams {
 // register-MMA kernel (extend_mma.cu): any shape the library accepts
 int extend_mma_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaStream_t st);
 
-// tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit KV, logit_cap == 0
+// tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit or FP8-E4M3 KV, logit_cap == 0
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb);
-int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st);
+int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st);
 
 }  // namespace b200attn

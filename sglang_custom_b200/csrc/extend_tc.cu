@@ -173,9 +173,15 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   prof.mark(4);
 }
 
-template <bool kBf16, int kEmu, bool kProf>
+// kBf16: MMA operand format (bf16 or f16).  kFp8: the pool holds e4m3 bytes; the producers expand them to f16 on
+// the way into shared memory (F2FP.F16.E4M3.UNPACK_B, exact; it issues on the ALU pipe and overlaps the MUFU
+// exponentials -- scripts/ubench/pipes.cu), so the MMA runs in f16 and kBf16 is false.  kQCvt: q/out are bf16 while
+// the MMA runs in f16 (bf16 model over an FP8 KV cache): Q is converted on its way into shared memory.
+template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false>
 __global__ void __launch_bounds__(kThreads, 1)
 extend_tc_kernel(const ExtendParams p, const int pair_heads) {
+  static_assert(!(kFp8 && kBf16) && !(kQCvt && kBf16), "FP8 KV runs the MMA in f16");
+  constexpr bool kOutBf16 = kBf16 || kQCvt;  // dtype of q and out in global memory
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms repeat every 1024 B
   const uint32_t bars = smem + kOffBar;
@@ -254,10 +260,19 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
         const uint16_t* src = ok ? qbase + static_cast<int64_t>(start + q0[t] + r) * p.q_tok_stride + ch * 8
                                  : reinterpret_cast<const uint16_t*>(p.q);
         const uint32_t dst = sq + (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
-        cp_async16(dst, src, ok ? 16 : 0);
+        if constexpr (kQCvt) {
+          uint4 w = ok ? __ldg(reinterpret_cast<const uint4*>(src)) : make_uint4(0u, 0u, 0u, 0u);
+          w.x = ptx::bf16x2_to_f16x2(w.x); w.y = ptx::bf16x2_to_f16x2(w.y);
+          w.z = ptx::bf16x2_to_f16x2(w.z); w.w = ptx::bf16x2_to_f16x2(w.w);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w) : "memory");
+        } else {
+          cp_async16(dst, src, ok ? 16 : 0);
+        }
       }
-      cp_async_commit();
-      cp_async_wait<0>();
+      if constexpr (!kQCvt) {
+        cp_async_commit();
+        cp_async_wait<0>();
+      }
       ptx::fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
       ptx::mbar_arrive(bar(Q_FULL));
     }
@@ -299,10 +314,10 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
 #pragma unroll
           for (int v4 = 0; v4 < 4; ++v4) {
             uint4 w;
-            w.x = pack2<kBf16>(__uint_as_float(o[8 * v4 + 0]) * inv, __uint_as_float(o[8 * v4 + 1]) * inv);
-            w.y = pack2<kBf16>(__uint_as_float(o[8 * v4 + 2]) * inv, __uint_as_float(o[8 * v4 + 3]) * inv);
-            w.z = pack2<kBf16>(__uint_as_float(o[8 * v4 + 4]) * inv, __uint_as_float(o[8 * v4 + 5]) * inv);
-            w.w = pack2<kBf16>(__uint_as_float(o[8 * v4 + 6]) * inv, __uint_as_float(o[8 * v4 + 7]) * inv);
+            w.x = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 0]) * inv, __uint_as_float(o[8 * v4 + 1]) * inv);
+            w.y = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 2]) * inv, __uint_as_float(o[8 * v4 + 3]) * inv);
+            w.z = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 4]) * inv, __uint_as_float(o[8 * v4 + 5]) * inv);
+            w.w = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 6]) * inv, __uint_as_float(o[8 * v4 + 7]) * inv);
             *reinterpret_cast<uint4*>(dst + c * 32 + v4 * 8) = w;
           }
         }
@@ -425,21 +440,9 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
     // loop-invariant registers instead of one per copy.
     const int pw = warp - 9;
     const int32_t* trow = p.req_to_token + load_index(p.req_pool_indices, p.idx_is_i64, req) * p.table_stride;
-    const int64_t row_bytes = p.pool_tok_stride * 2;
-    const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
-    const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
-    const int sub = lane >> 4;                       // which row of the pair
-    const int ch = lane & 15;                        // 16-byte chunk of the 256-byte row
     constexpr int kGroups = 6;                       // groups per producer warp (the last one only for pw == 0)
-    uint32_t dst_q[4];                               // destination of (group pw, pair q) relative to the tile base
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int r = 8 * pw + 2 * q + sub;
-      dst_q[q] = (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
-    }
     // Page-table slots: lane i of load c holds the slot of row 8 * (pw + 3 * (4 c + i / 8)) + i % 8 -- the rows of
-    // this warp only, two coalesced-by-eight loads per tile, fetched one tile ahead; the copy of (group k', pair q)
-    // takes its slot from lane 8 * (k' % 4) + 2 q + sub of register k' / 4 with a shuffle.
+    // this warp only, two coalesced-by-eight loads per tile, fetched one tile ahead.
     int sreg[2];
     auto load_slots = [&](int j) {
 #pragma unroll
@@ -449,42 +452,125 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
         sreg[c] = (m < 16 && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
       }
     };
-    int slot[4 * kGroups];
-    auto spread_slots = [&]() {
+    if constexpr (!kFp8) {
+      const int64_t row_bytes = p.pool_tok_stride * 2;
+      const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+      const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+      const int sub = lane >> 4;                       // which row of the pair
+      const int ch = lane & 15;                        // 16-byte chunk of the 256-byte row
+      uint32_t dst_q[4];                               // destination of (group pw, pair q) relative to the tile base
 #pragma unroll
-      for (int kq = 0; kq < 4 * kGroups; ++kq) {
-        const int kp = kq >> 2, q = kq & 3;
-        slot[kq] = __shfl_sync(0xffffffffu, sreg[kp >> 2], 8 * (kp & 3) + 2 * q + sub);
+      for (int q = 0; q < 4; ++q) {
+        const int r = 8 * pw + 2 * q + sub;
+        dst_q[q] = (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
       }
-    };
-    auto gather = [&](const uint8_t* base, uint32_t tile) {
+      // the copy of (group k', pair q) takes its slot from lane 8 * (k' % 4) + 2 q + sub of register k' / 4
+      int slot[4 * kGroups];
+      auto spread_slots = [&]() {
 #pragma unroll
-      for (int kq = 0; kq < 4 * kGroups; ++kq) {
-        const int kp = kq >> 2, q = kq & 3;
-        if (pw + 3 * kp < 16)  // warp-uniform
-          cp_async16(tile + dst_q[q] + kp * 3072, base + static_cast<int64_t>(slot[kq]) * row_bytes);
-      }
-    };
-    load_slots(0);
-    prof.begin();
+        for (int kq = 0; kq < 4 * kGroups; ++kq) {
+          const int kp = kq >> 2, q = kq & 3;
+          slot[kq] = __shfl_sync(0xffffffffu, sreg[kp >> 2], 8 * (kp & 3) + 2 * q + sub);
+        }
+      };
+      auto gather = [&](const uint8_t* base, uint32_t tile) {
+#pragma unroll
+        for (int kq = 0; kq < 4 * kGroups; ++kq) {
+          const int kp = kq >> 2, q = kq & 3;
+          if (pw + 3 * kp < 16)  // warp-uniform
+            cp_async16(tile + dst_q[q] + kp * 3072, base + static_cast<int64_t>(slot[kq]) * row_bytes);
+        }
+      };
+      load_slots(0);
+      prof.begin();
 #pragma unroll 1
-    for (int j = 0; j < n; ++j) {
-      const int b = j & 1, u = j >> 1;
-      spread_slots();
-      if (j + 1 < n) load_slots(j + 1);  // issued before this tile's copies so that it never queues behind them
-      prof.mark(0);
-      // K_j
-      ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
-      prof.mark(1);
-      gather(kbase, smem + kOffK + b * kTileBytes);
-      ptx::cp_async_mbar_arrive_noinc(bar(K_FULL + b));
-      prof.mark(2);
-      // V_j
-      ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
-      prof.mark(3);
-      gather(vbase, smem + kOffV + b * kTileBytes);
-      ptx::cp_async_mbar_arrive_noinc(bar(V_FULL + b));
-      prof.mark(4);
+      for (int j = 0; j < n; ++j) {
+        const int b = j & 1, u = j >> 1;
+        spread_slots();
+        if (j + 1 < n) load_slots(j + 1);  // issued before this tile's copies so that it never queues behind them
+        prof.mark(0);
+        // K_j
+        ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
+        prof.mark(1);
+        gather(kbase, smem + kOffK + b * kTileBytes);
+        ptx::cp_async_mbar_arrive_noinc(bar(K_FULL + b));
+        prof.mark(2);
+        // V_j
+        ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
+        prof.mark(3);
+        gather(vbase, smem + kOffV + b * kTileBytes);
+        ptx::cp_async_mbar_arrive_noinc(bar(V_FULL + b));
+        prof.mark(4);
+      }
+    } else {
+      // FP8-E4M3 pool: a row of one kv head is 128 bytes; a warp instruction loads four rows (8 lanes x 16 B each),
+      // every lane expands its 16 e4m3 values to 16 f16 (two 16-byte chunks of the 256-byte shared-memory row) and
+      // stores them into the same UMMA canonical 128B-swizzle layout the 16-bit path fills with LDGSTS.  The loads of
+      // a half tile (three 8-row groups = six warp loads) are all issued before the first conversion.  Register
+      // stores go through the generic proxy: fence.proxy.async, then a plain mbarrier arrive.
+      const int64_t row_bytes = p.pool_tok_stride;
+      const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * kTile + (lane & 7) * 16;
+      const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * kTile + (lane & 7) * 16;
+      const int sub = lane >> 3;                       // which row of the quad
+      const int c0 = 2 * (lane & 7);                   // first of the two 16-byte f16 chunks this lane produces
+      uint32_t dst_q[2];                               // destination of (group pw, quad q), chunk c0; chunk c0+1 is ^ 16
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int r = 8 * pw + 4 * q + sub;
+        dst_q[q] = (c0 >> 3) * kHalfBytes + r * 128 + (((c0 & 7) ^ (r & 7)) << 4);
+      }
+      int scur[2];  // this tile's slots (sreg holds the next tile's); spread by shuffle at the point of use
+      // the twelve warp loads of a tile share are issued before the wait for the empty buffer: registers do not
+      // depend on shared memory, so the L2 / HBM latency overlaps the MMAs still reading the previous tile
+      auto issue_loads = [&](const uint8_t* base, uint4 (&w)[12]) {
+#pragma unroll
+        for (int kq = 0; kq < 12; ++kq) {
+          const int kp = kq >> 1;
+          if (pw + 3 * kp < 16) {  // warp-uniform
+            const int sl = __shfl_sync(0xffffffffu, scur[kp >> 2], 8 * (kp & 3) + 4 * (kq & 1) + sub);
+            w[kq] = ld_nc_16(base + static_cast<int64_t>(sl) * row_bytes);
+          }
+        }
+      };
+      auto expand_store = [&](uint32_t tile, const uint4 (&w)[12]) {
+#pragma unroll
+        for (int kq = 0; kq < 12; ++kq) {
+          const int kp = kq >> 1, q = kq & 1;
+          if (pw + 3 * kp < 16) {
+            const uint32_t d = tile + dst_q[q] + kp * 3072;
+            const uint32_t in[4] = {w[kq].x, w[kq].y, w[kq].z, w[kq].w};
+            uint32_t o[8];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              o[2 * e] = e4m3x2_to_f16x2(static_cast<uint16_t>(in[e] & 0xffffu));
+              o[2 * e + 1] = e4m3x2_to_f16x2(static_cast<uint16_t>(in[e] >> 16));
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(d), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(d ^ 16u), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
+          }
+        }
+      };
+      load_slots(0);
+      prof.begin();
+      uint4 w[12];
+      scur[0] = sreg[0]; scur[1] = sreg[1];
+      if (n > 0) issue_loads(kbase, w);
+#pragma unroll 1
+      for (int j = 0; j < n; ++j) {
+        const int b = j & 1, u = j >> 1;
+        if (j + 1 < n) load_slots(j + 1);
+        ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
+        expand_store(smem + kOffK + b * kTileBytes, w);
+        issue_loads(vbase, w);  // V_j on its way while K_j is published
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(bar(K_FULL + b));
+        ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
+        expand_store(smem + kOffV + b * kTileBytes, w);
+        scur[0] = sreg[0]; scur[1] = sreg[1];
+        if (j + 1 < n) issue_loads(kbase, w);  // K_{j+1}
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(bar(V_FULL + b));
+      }
     }
     prof.flush(p.prof, warp, lane);
   }
@@ -501,7 +587,7 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
 }  // namespace tc
 
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb) {
-  return D == 128 && kvb == 2 && p.logit_cap == 0.f && p.Hq >= 1 && (p.pool_tok_stride * 2) % 16 == 0;
+  return D == 128 && (kvb == 2 || kvb == 1) && p.logit_cap == 0.f && p.Hq >= 1 && (p.pool_tok_stride * kvb) % 16 == 0;
 }
 
 namespace {
@@ -519,9 +605,13 @@ KernelFn pick_kernel(int emu, bool prof) {
 }
 }  // namespace
 
-int extend_tc_launch(const ExtendParams& p, bool q_bf16, cudaStream_t st) {
+int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
   const int emu = (p.exp_emu >= 0 && p.exp_emu <= 3) ? p.exp_emu : 2;
-  KernelFn kern = q_bf16 ? pick_kernel<true>(emu, p.prof != nullptr) : pick_kernel<false>(emu, p.prof != nullptr);
+  KernelFn kern;
+  if (kvb == 1)  // FP8-E4M3 pool: f16 MMA, e4m3 expanded by the producers; bf16 q converted on load
+    kern = q_bf16 ? tc::extend_tc_kernel<false, 0, false, true, true> : tc::extend_tc_kernel<false, 0, false, true, false>;
+  else
+    kern = q_bf16 ? pick_kernel<true>(emu, p.prof != nullptr) : pick_kernel<false>(emu, p.prof != nullptr);
   // opt in to the large dynamic shared memory once per kernel instance (cheap host call, no device sync)
   B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes));
   const int pair_heads = (p.G % 2 == 0) ? 1 : 0;

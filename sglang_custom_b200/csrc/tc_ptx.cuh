@@ -113,6 +113,14 @@ __device__ __forceinline__ float2 exp2_poly2(float2 x) {
 }
 
 // one lane of a converged warp (the same lane every time): the issuer of tcgen05.mma / tcgen05.commit
+// packed bf16x2 -> packed f16x2 (round to nearest, saturating to the largest finite f16)
+__device__ __forceinline__ uint32_t bf16x2_to_f16x2(uint32_t x) {
+  const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;\n" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

@@ -76,6 +76,23 @@ def test_both_extend_kernels_agree_with_fp64(impl, lens, ext, device):
 
 
 @pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05])
+@pytest.mark.parametrize("kw", [dict(kv_scale=1.0), dict(kv_scale=0.1135), dict(kv_scale=0.1135, page_size=16),
+                                dict(kv_scale=0.5, dtype=torch.float16)])
+def test_fp8_kv_extend_both_kernels(impl, kw, device):
+    """FP8-E4M3 KV cache under extend: the tcgen05 kernel expands e4m3 to f16 in its producer warps (exact) and
+    runs the MMA in f16; the register-MMA kernel expands in registers.  Both against the fp64 restatement on the
+    same pool bytes and against oracle #1 on the dequantised pool."""
+    lens, ext = [640, 333, 1100, 130], [256, 333, 129, 2]
+    case = synth.make_case(len(lens), 16, 2, 128, lens, extend_lens=ext, fp8=True, seed=4242, **kw)
+    kp, vp = H.pool_after_write(case)
+    out, lse = _direct(case, device, kp, vp, impl, want_lse=True)
+    want, want_lse = H.exact_extend(case, kp, vp, return_lse=True)
+    H.assert_close(out, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"fp8 impl={impl}", rel=True)
+    assert torch.allclose(lse.cpu(), want_lse, atol=2e-3, rtol=1e-4)
+    H.assert_close(out, H.oracle_extend(case, kp, vp), what="fp8 vs torch_native on the dequantised pool")
+
+
+@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05])
 def test_extend_non_causal_encoder_only(impl, device):
     """ENCODER_ONLY layers attend bidirectionally (torch_native_backend.py:206-208)."""
     case = synth.make_case(2, 8, 2, 128, [200, 131], extend_lens=[200, 131], seed=9)
