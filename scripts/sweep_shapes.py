@@ -54,6 +54,7 @@ def main():
         ragged = torch.randint(2048, 4097, (256,), generator=g).tolist()
         run("C2 ragged U[2048,4096]", 256, 32, 8, 128, ragged, False, (148,))
         run("C2 page16", 256, 32, 8, 128, [4096] * 256, False, (148,), page_size=16)
+        run("C2 arange table (sequential slots)", 256, 32, 8, 128, [4096] * 256, False, (148,), table="arange")
     if which in ("all", "c4"):
         for tp, (hq, hkv) in ((2, (32, 4)), (4, (16, 2)), (8, (8, 1))):
             run(f"C4 fp8 tp{tp} {hq}/{hkv} bs512 ctx8192", 512, hq, hkv, 128, [8192] * 512, True, (148, 296))
