@@ -5,22 +5,23 @@
 // GPU designs it supersedes: triton_ops/decode_attention.py:45-552 (stage1 + stage2) and the
 // sgl-kernel CPU flash-decoding sgl-kernel/csrc/cpu/decode.cpp:863-1373.
 //
-// Design (HBM-bound: the job is to keep >= 64 KiB of row gathers in flight per SM)
-//   * persistent grid: n_ctas CTAs (one or two per SM); the device-side plan
-//     (decode_plan.cu) hands every CTA an equal share of the flattened
-//     16-token units of the batch, so ragged batches stay balanced without a host sync.
-//   * a CTA owns HB kv heads (HB = 8 for Llama-3-8B: the K row of one token for
-//     all 8 heads is one contiguous 2 KiB segment of the pool) and walks its
-//     share in tiles of NT tokens; rows are gathered straight from the pool through
-//     req_to_token with 16-byte cp.async (LDGSTS) into a 3-stage XOR-swizzled
-//     shared-memory ring -- no flattened kv_indices copy is ever built.
-//   * warp (hb, ts) computes 16 tokens of head hb per tile: the GQA group is
-//     packed as the M dimension of mma.sync.m16n8k16 (S = Q K^T, O += P V),
-//     fp32 online softmax with quad shuffles; FP8-E4M3 K/V are dequantised in
-//     registers (cvt.rn.f16x2.e4m3x2) on their way into the MMA.
-//   * a request handled entirely by one CTA is normalised and written directly;
-//     otherwise the CTA writes a normalised fp32 partial + LSE and the merge
-//     kernel (below) combines the pieces.
+// Design (HBM-bound: the job is to keep the row gathers streaming and the per-tile math off their critical path)
+//   * persistent grid: n_ctas CTAs (one per SM); the device-side plan (decode_plan.cu) hands every CTA an equal
+//     share of the flattened 16-token units of the batch, so ragged batches stay balanced without a host sync.
+//   * a CTA owns HB kv heads (HB = 8 for Llama-3-8B: the K row of one token for all 8 heads is one contiguous
+//     2 KiB segment of the pool) and walks its share in tiles of NT tokens; rows are gathered straight from the
+//     pool through req_to_token with 16-byte cp.async (LDGSTS) into a 3..6-stage XOR-swizzled shared-memory
+//     ring -- no flattened kv_indices copy is ever built.
+//   * warp-specialised: warps 8-11 are producers (gather only), warps 0-7 consumers; stages are handed over with
+//     full/empty mbarriers, registers re-balanced with setmaxnreg.  (The first cut was monolithic: every warp
+//     issued its share of the gather, then computed, one __syncthreads per tile -- 6.09 TB/s at C2 against
+//     6.92 TB/s for this design; ncu showed 31 % of warp time at that barrier and a ~2000-cycle serial chain per
+//     64 KiB tile against a 2560-cycle HBM budget.)
+//   * consumer warp (hb, ts) computes 16 tokens of head hb per tile: the GQA group is packed as the M dimension
+//     of mma.sync.m16n8k16 (S = Q K^T, O += P V), fp32 online softmax with quad shuffles; FP8-E4M3 K/V are
+//     dequantised in registers (cvt.rn.f16x2.e4m3x2) on their way into the MMA.
+//   * a request handled entirely by one CTA is normalised and written directly; otherwise the CTA writes a
+//     normalised fp32 partial + LSE and the merge kernel (below) combines the pieces.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -51,8 +52,9 @@ struct DecodeParams {
   float v_scale;
 };
 
-constexpr int kDecodeThreads = 256;
-constexpr int kDecodeWarps = 8;
+constexpr int kDecodeWarps = 8;                                 // consumer warps
+constexpr int kProducerThreads = 128;                           // 4 producer warps
+constexpr int kDecodeThreads = kDecodeWarps * 32 + kProducerThreads;
 constexpr int kMaxSeg = 32;
 
 template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE>
@@ -66,15 +68,18 @@ struct DecodeCfg {
   static constexpr int TILEB = NT * ROWB;            // bytes of a K (or V) tile
   static constexpr int STAGEB = 2 * TILEB;
   static constexpr int CHUNKS = NT * CPR;            // 16-byte chunks per K tile
-  static constexpr int ITERS = CHUNKS / kDecodeThreads;
+  static constexpr int P_ITERS = CHUNKS / kProducerThreads;
+  static_assert(CHUNKS % kProducerThreads == 0, "tile must divide over the producer warps");
   static constexpr int SWZ = CPH >= 8 ? 7 : (CPH - 1);
-  static_assert(CHUNKS % kDecodeThreads == 0, "tile must divide over the CTA");
   static constexpr int RED_ROWS = 16;
-  // the cross-warp merge buffer aliases the stage that was consumed last (see the tree merge)
+  // cross-warp merge buffer of the TS warps of a head (dedicated: the producers refill stages asynchronously)
   static constexpr int REDB = (TS > 1) ? (kDecodeWarps / 2) * RED_ROWS * (D + 2) * 4 : 0;
-  static constexpr bool RED_ALIAS = REDB <= STAGEB;  // else a dedicated buffer after the index ring
-  static constexpr int IDXB = (NSTAGE + 1) * NT * 4;
-  static constexpr int SMEM = NSTAGE * STAGEB + IDXB + (RED_ALIAS ? 0 : REDB) + 128;
+  static constexpr int IDXB = 2 * NT * 4;            // double-buffered token-slot ring
+  static constexpr int BARB = 2 * NSTAGE * 8;        // full[NSTAGE], empty[NSTAGE]
+  static constexpr int OFF_RED = NSTAGE * STAGEB;
+  static constexpr int OFF_IDX = OFF_RED + REDB;
+  static constexpr int OFF_BAR = OFF_IDX + IDXB;
+  static constexpr int SMEM = OFF_BAR + BARB + 128;
 };
 
 struct Segment {
@@ -86,481 +91,21 @@ struct Segment {
 };
 
 // ---------------------------------------------------------------------------------------
-template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE>
-__global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeParams p) {
-  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
-  constexpr bool kFp8 = (KVB == 1);
-  constexpr bool kMmaBf16 = kQBf16 && !kFp8;  // fp8 K/V are dequantised to f16 (exact)
-  constexpr int TS = Cfg::TS, NT = Cfg::NT;
-  constexpr int KSTEPS = D / 16;
-  constexpr int NBLK = D / 8;
-
-  extern __shared__ __align__(128) uint8_t smem[];
-  uint8_t* stage_base = smem;
-  int32_t* idx_ring = reinterpret_cast<int32_t*>(smem + NSTAGE * Cfg::STAGEB);
-  __shared__ Segment segs[kMaxSeg];
-  __shared__ int n_segs_sh;
-  __shared__ int next_req_sh, next_unit_sh;
-
-  const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
-  const int hb = warp % HB;   // head within the CTA's head block
-  const int ts = warp / HB;   // token sub-tile
-  const int qd = lane & 3;    // quad lane
-  const int row = lane >> 2;  // MMA row 0..7
-  const int cta = blockIdx.x;
-  const int kv_head = blockIdx.y * HB + hb;
-  const int G = p.G;
-
-  const int32_t* plan = p.plan;
-  const int total_units = plan[kPlanTotalUnits];
-  const int W = plan[kPlanUnitsPerCta];
-  const int bs = p.bs;
-  const int32_t* cum = plan + kPlanHeader;               // [bs + 1]
-  const int32_t* first_req = plan + kPlanHeader + bs + 1; // [n_ctas]
-  const int u_begin = cta * W;
-  if (u_begin >= total_units) return;
-  const int u_end = min(u_begin + W, total_units);
-
-  if (tid == 0) {
-    next_req_sh = first_req[cta];
-    next_unit_sh = u_begin;
-  }
-  __syncthreads();
-
-  const uint8_t* kpool = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
-  const uint8_t* vpool = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
-  const int64_t pool_row_bytes = p.pool_tok_stride * KVB;
-
-  while (true) {
-    // ---------------- build the next batch of segments (thread 0), at most kMaxSeg
-    if (tid == 0) {
-      int i = next_req_sh, u = next_unit_sh, n = 0;
-      while (u < u_end && n < kMaxSeg) {
-        while (cum[i + 1] <= u) ++i;
-        const int c0 = cum[i], c1 = cum[i + 1];
-        const int seg_end = min(c1, u_end);
-        const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
-        Segment s;
-        s.batch = i;
-        s.tok_begin = (u - c0) * kUnit;
-        s.tok_end = min((seg_end - c0) * kUnit, L);
-        const bool is_first = (u == c0), is_last = (seg_end == c1);
-        s.slot = (is_first && is_last) ? -1 : (is_first ? 2 * cta + 1 : 2 * cta);
-        s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride;
-        segs[n++] = s;
-        u = seg_end;
-      }
-      n_segs_sh = n;
-      next_req_sh = i;
-      next_unit_sh = u;
-    }
-    __syncthreads();
-    const int n_segs = n_segs_sh;
-    if (n_segs == 0) break;
-
-    // ---------------- producer cursor: walks (segment, tile) pairs of this batch
-    int p_seg = 0, p_tile = 0;  // next tile to issue
-    int p_count = 0;            // tiles issued so far
-    int p_idx_seg = 0, p_idx_tile = 0, p_idx_count = 0;  // next tile whose indices get staged
-
-    auto seg_tiles = [&](int s) { return (segs[s].tok_end - segs[s].tok_begin + NT - 1) / NT; };
-
-    // Token slots of one tile -> index ring (first NT threads), in two steps so that the page-table load is never
-    // waited for: fetch_indices() issues the load into a register, store_indices() -- one tile step later, just
-    // before the barrier that publishes the ring -- writes it to shared memory.  (The first cut stored right
-    // after the load: the STS stalled on the full global-load latency every step, 19 % of all stall samples in
-    // profiles/r01_decode_fp8_full.)
-    int32_t pend_slot = -1;
-    int pend_pos = -1;
-    auto fetch_indices = [&]() {
-      if (p_idx_seg >= n_segs) return;
-      if (tid < NT) {
-        const Segment& s = segs[p_idx_seg];
-        const int tok = s.tok_begin + p_idx_tile * NT + tid;
-        pend_slot = (tok < s.tok_end) ? __ldg(p.req_to_token + s.table_off + tok) : -1;
-        pend_pos = (p_idx_count % (NSTAGE + 1)) * NT + tid;
-      }
-      ++p_idx_count;
-      if (++p_idx_tile >= seg_tiles(p_idx_seg)) { p_idx_tile = 0; ++p_idx_seg; }
-    };
-    auto store_indices = [&]() {
-      if (pend_pos >= 0) {
-        idx_ring[pend_pos] = pend_slot;
-        pend_pos = -1;
-      }
-    };
-    auto stage_indices = [&]() {  // prologue: fetch + store at once
-      fetch_indices();
-      store_indices();
-    };
-
-    // issue the gathers of one tile (all threads); always commits a group
-    auto issue_tile = [&]() {
-      if (p_seg < n_segs) {
-        const int32_t* idx = idx_ring + (p_count % (NSTAGE + 1)) * NT;
-        uint8_t* kst = stage_base + (p_count % NSTAGE) * Cfg::STAGEB;
-        const uint32_t k_s = smem_u32(kst), v_s = k_s + Cfg::TILEB;
-#pragma unroll
-        for (int it = 0; it < Cfg::ITERS; ++it) {
-          const int c = it * kDecodeThreads + tid;
-          const int tok = c / Cfg::CPR;
-          const int cr = c % Cfg::CPR;
-          const int head = cr / Cfg::CPH, ch = cr % Cfg::CPH;
-          const int32_t slot = idx[tok];
-          const int valid = slot >= 0 ? 16 : 0;
-          const int64_t src = static_cast<int64_t>(slot >= 0 ? slot : 0) * pool_row_bytes + cr * 16;
-          const uint32_t dst = tok * Cfg::ROWB + head * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4);
-          cp_async16(k_s + dst, kpool + src, valid);
-          cp_async16(v_s + dst, vpool + src, valid);
-        }
-        ++p_count;
-        if (++p_tile >= seg_tiles(p_seg)) { p_tile = 0; ++p_seg; }
-      }
-      cp_async_commit();
-    };
-
-    // prologue: indices for the first NSTAGE tiles, gathers for the first NSTAGE-1
-#pragma unroll
-    for (int s = 0; s < NSTAGE; ++s) stage_indices();
-    __syncthreads();
-#pragma unroll
-    for (int s = 0; s < NSTAGE - 1; ++s) issue_tile();
-
-    int c_count = 0;  // tiles consumed
-    for (int sg = 0; sg < n_segs; ++sg) {
-      const Segment seg = segs[sg];
-      const int ntiles = (seg.tok_end - seg.tok_begin + NT - 1) / NT;
-
-      // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
-      uint32_t qa[KSTEPS][4];
-      {
-        const uint16_t* qrow0 = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride +
-                                static_cast<int64_t>(kv_head * G + row) * D;
-        const uint16_t* qrow1 = qrow0 + 8 * D;
-        const bool v0 = row < G, v1 = !kG8 && (row + 8 < G);
-#pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks) {
-          uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-          if constexpr (!kFp8) {
-            if (v0) {
-              a0 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 2 * qd);
-              a2 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 8 + 2 * qd);
-            }
-            if (v1) {
-              a1 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 2 * qd);
-              a3 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 8 + 2 * qd);
-            }
-          } else {
-            // fp8 K: a thread's ldmatrix register holds d = 16*ks + 4*qd + {0,1,2,3}; the
-            // contraction index is permuted identically on the Q side.
-            if (v0) {
-              const uint2 t = *reinterpret_cast<const uint2*>(qrow0 + ks * 16 + 4 * qd);
-              a0 = t.x; a2 = t.y;
-            }
-            if (v1) {
-              const uint2 t = *reinterpret_cast<const uint2*>(qrow1 + ks * 16 + 4 * qd);
-              a1 = t.x; a3 = t.y;
-            }
-            if constexpr (kQBf16) {  // bf16 -> f16 (saturating), the MMA runs in f16 for fp8 KV
-              auto cv = [](uint32_t x) {
-                const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
-                const float l2 = fminf(fmaxf(lo, -65504.f), 65504.f), h2 = fminf(fmaxf(hi, -65504.f), 65504.f);
-                return pack2<false>(l2, h2);
-              };
-              a0 = cv(a0); a1 = cv(a1); a2 = cv(a2); a3 = cv(a3);
-            }
-          }
-          qa[ks][0] = a0; qa[ks][1] = a1; qa[ks][2] = a2; qa[ks][3] = a3;
-        }
-      }
-
-      float o[NBLK][4];
-#pragma unroll
-      for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
-      float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-
-      for (int t = 0; t < ntiles; ++t) {
-        cp_async_wait<NSTAGE - 2>();
-        store_indices();   // slots fetched during the previous step (made visible by the barrier)
-        __syncthreads();
-        issue_tile();      // refills the stage consumed in the previous iteration
-        fetch_indices();   // page-table load for the tile after that; lands while this step computes
-
-        const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
-        const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
-        const uint32_t k_s = smem_u32(stage_base + (c_count % NSTAGE) * Cfg::STAGEB);
-        const uint32_t v_s = k_s + Cfg::TILEB;
-        ++c_count;
-        if (nvalid <= 0) continue;
-
-        // ---- S = Q K^T for 16 tokens (2 n-blocks of 8)
-        float s[2][4];
-#pragma unroll
-        for (int nb = 0; nb < 2; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
-        if constexpr (!kFp8) {
-#pragma unroll
-          for (int ks = 0; ks < KSTEPS; ++ks) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj >> 1) * 8 + mr;
-            const int ch = 2 * ks + (mj & 1);
-            uint32_t r[4];
-            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-            mma_16816<kMmaBf16>(s[0], qa[ks], r[0], r[1]);
-            mma_16816<kMmaBf16>(s[1], qa[ks], r[2], r[3]);
-          }
-        } else {
-          // fp8: one 16-byte chunk = 16 d; matrices (tok 0-7, ch), (tok 8-15, ch), (tok 0-7, ch+1), (tok 8-15, ch+1)
-#pragma unroll
-          for (int kp = 0; kp < KSTEPS / 2; ++kp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * kp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const uint32_t r0 = r[2 * half], r1 = r[2 * half + 1];
-              const int ks = 2 * kp + half;
-              mma_16816<false>(s[0], qa[ks], e4m3x2_to_f16x2(r0 & 0xffff), e4m3x2_to_f16x2(r0 >> 16));
-              mma_16816<false>(s[1], qa[ks], e4m3x2_to_f16x2(r1 & 0xffff), e4m3x2_to_f16x2(r1 >> 16));
-            }
-          }
-        }
-
-        // ---- scale, cap, mask, online softmax (log2 domain)
-#pragma unroll
-        for (int nb = 0; nb < 2; ++nb) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x;
-            if (p.logit_cap > 0.f) {
-              x = p.logit_cap * fast_tanh(s[nb][e] * p.scale_raw / p.logit_cap) * kLog2e;
-            } else {
-              x = s[nb][e] * p.scale_log2;
-            }
-            const int col = nb * 8 + 2 * qd + (e & 1);
-            s[nb][e] = (col < nvalid) ? x : -INFINITY;
-          }
-        }
-        float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        const float mn0 = fmaxf(m0, mx0);  // finite: at least one valid column
-        const float al0 = fast_exp2(m0 - mn0);
-        m0 = mn0;
-        float p00 = fast_exp2(s[0][0] - mn0), p01 = fast_exp2(s[0][1] - mn0);
-        float p10 = fast_exp2(s[1][0] - mn0), p11 = fast_exp2(s[1][1] - mn0);
-        l0 = l0 * al0 + (p00 + p01 + p10 + p11);
-        uint32_t pa[4];
-        pa[0] = pack2<kMmaBf16>(p00, p01);
-        pa[2] = pack2<kMmaBf16>(p10, p11);
-        float al1 = 1.f;
-        if constexpr (!kG8) {
-          float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
-          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-          const float mn1 = fmaxf(m1, mx1);
-          al1 = fast_exp2(m1 - mn1);
-          m1 = mn1;
-          const float q00 = fast_exp2(s[0][2] - mn1), q01 = fast_exp2(s[0][3] - mn1);
-          const float q10 = fast_exp2(s[1][2] - mn1), q11 = fast_exp2(s[1][3] - mn1);
-          l1 = l1 * al1 + (q00 + q01 + q10 + q11);
-          pa[1] = pack2<kMmaBf16>(q00, q01);
-          pa[3] = pack2<kMmaBf16>(q10, q11);
-        } else {
-          pa[1] = 0u; pa[3] = 0u;
-        }
-#pragma unroll
-        for (int nb = 0; nb < NBLK; ++nb) {
-          o[nb][0] *= al0; o[nb][1] *= al0;
-          if constexpr (!kG8) { o[nb][2] *= al1; o[nb][3] *= al1; }
-        }
-
-        // ---- O += P V
-        if constexpr (!kFp8) {
-#pragma unroll
-          for (int jp = 0; jp < NBLK / 2; ++jp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * jp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-            mma_16816<kMmaBf16>(o[2 * jp], pa, r[0], r[1]);
-            mma_16816<kMmaBf16>(o[2 * jp + 1], pa, r[2], r[3]);
-          }
-        } else {
-          // fp8 V: a transposed b16 ldmatrix hands a thread (tok 2qd, d pair), (tok 2qd+1, d pair);
-          // regroup bytes so each half-word is one d for two consecutive tokens.
-          // chunk c (16 d) -> n-block "even d" o[4c'+..]; accumulator column order is fixed up at the store.
-#pragma unroll
-          for (int cp = 0; cp < D / 32; ++cp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * cp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const uint32_t lo = r[2 * half], hi = r[2 * half + 1];  // tokens 0-7, tokens 8-15
-              const uint32_t e_lo = __byte_perm(lo, 0, 0x0020), o_lo = __byte_perm(lo, 0, 0x0031);
-              const uint32_t e_hi = __byte_perm(hi, 0, 0x0020), o_hi = __byte_perm(hi, 0, 0x0031);
-              const int c = 2 * cp + half;  // 16-d chunk
-              mma_16816<false>(o[2 * c], pa, e4m3x2_to_f16x2(e_lo), e4m3x2_to_f16x2(e_hi));
-              mma_16816<false>(o[2 * c + 1], pa, e4m3x2_to_f16x2(o_lo), e4m3x2_to_f16x2(o_hi));
-            }
-          }
-        }
-      }  // tiles
-
-      // ---- finish the piece: reduce l over the quad, merge the TS warps of a head, store
-      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-      if constexpr (!kG8) {
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-      }
-      if constexpr (TS > 1) {
-        // tree merge: in each round the upper half of the token sub-tiles hands its state to the lower half
-        constexpr int RSTRIDE = D + 2;
-        // the stage consumed last is free until the next issue_tile(), which sits behind a barrier
-        float* red = Cfg::RED_ALIAS
-                         ? reinterpret_cast<float*>(stage_base + ((c_count + NSTAGE - 1) % NSTAGE) * Cfg::STAGEB)
-                         : reinterpret_cast<float*>(smem + NSTAGE * Cfg::STAGEB + Cfg::IDXB);
-#pragma unroll
-        for (int half = TS / 2; half >= 1; half >>= 1) {
-          __syncthreads();
-          if (ts >= half && ts < 2 * half) {
-            float* dst = red + ((ts - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
-#pragma unroll
-            for (int nb = 0; nb < NBLK; ++nb) {
-              *reinterpret_cast<float2*>(dst + row * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][0], o[nb][1]);
-              if constexpr (!kG8)
-                *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][2], o[nb][3]);
-            }
-            if (qd == 0) {
-              *reinterpret_cast<float2*>(dst + row * RSTRIDE + D) = make_float2(m0, l0);
-              if constexpr (!kG8) *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + D) = make_float2(m1, l1);
-            }
-          }
-          __syncthreads();
-          if (ts < half) {
-            const float* src = red + (ts * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
-            {
-              const float2 ml = *reinterpret_cast<const float2*>(src + row * RSTRIDE + D);
-              const float mn = fmaxf(m0, ml.x);
-              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m0 - mn);
-              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
-              m0 = mn; l0 = l0 * a + ml.y * b;
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb) {
-                const float2 x = *reinterpret_cast<const float2*>(src + row * RSTRIDE + nb * 8 + 2 * qd);
-                o[nb][0] = o[nb][0] * a + x.x * b;
-                o[nb][1] = o[nb][1] * a + x.y * b;
-              }
-            }
-            if constexpr (!kG8) {
-              const float2 ml = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + D);
-              const float mn = fmaxf(m1, ml.x);
-              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m1 - mn);
-              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
-              m1 = mn; l1 = l1 * a + ml.y * b;
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb) {
-                const float2 x = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + nb * 8 + 2 * qd);
-                o[nb][2] = o[nb][2] * a + x.x * b;
-                o[nb][3] = o[nb][3] * a + x.y * b;
-              }
-            }
-          }
-        }
-      }
-
-      if (ts == 0) {
-#pragma unroll
-        for (int rr = 0; rr < (kG8 ? 1 : 2); ++rr) {
-          const int r = row + rr * 8;
-          if (r >= G) continue;
-          const float m = rr ? m1 : m0, l = rr ? l1 : l0;
-          const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
-          const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
-          const int head = kv_head * G + r;
-          if (seg.slot < 0) {
-            uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
-                            static_cast<int64_t>(head) * D;
-            if constexpr (!kFp8) {
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb)
-                *reinterpret_cast<uint32_t*>(dst + nb * 8 + 2 * qd) =
-                    pack2<kQBf16>(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
-            } else {
-#pragma unroll
-              for (int c = 0; c < D / 16; ++c) {  // thread holds d = 16c + 4qd + {0,2} (even blk), {1,3} (odd blk)
-                const uint32_t w0 = pack2<kQBf16>(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv);
-                const uint32_t w1 = pack2<kQBf16>(o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
-                *reinterpret_cast<uint2*>(dst + c * 16 + 4 * qd) = make_uint2(w0, w1);
-              }
-            }
-            if (p.lse_out != nullptr && qd == 0) p.lse_out[static_cast<int64_t>(seg.batch) * p.Hq + head] = lse;
-          } else {
-            float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D;
-            if constexpr (!kFp8) {
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb)
-                *reinterpret_cast<float2*>(dst + nb * 8 + 2 * qd) =
-                    make_float2(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
-            } else {
-#pragma unroll
-              for (int c = 0; c < D / 16; ++c)
-                *reinterpret_cast<float4*>(dst + c * 16 + 4 * qd) =
-                    make_float4(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv,
-                                o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
-            }
-            if (qd == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
-          }
-        }
-      }
-    }  // segments
-    cp_async_wait<0>();
-    __syncthreads();
-  }
-}
-
-// ---------------------------------------------------------------------------------------
-// Warp-specialised decode kernel (the default).  The per-tile math is the one above; what changes is who feeds it:
+// The decode kernel.
 //   * warps 0-7  = consumers: wait for a stage on its `full` mbarrier, compute, release it on `empty` -- no CTA-wide
-//     barrier and no gather issue on their critical path (ncu of the monolithic kernel: 31 % of warp time at the
-//     per-tile __syncthreads, 23 % in fixed-latency dependency stalls of a ~2000-cycle serial chain per 64 KiB
-//     tile, against a 2560-cycle HBM budget -- profiles/r01_ncu_decode_c2.txt);
+//     barrier and no gather issue on their critical path;
 //   * warps 8-11 = producers: gather the K/V rows of a tile through req_to_token with 16-byte cp.async as soon
 //     as the stage is released; completion is counted on the `full` mbarrier (cp.async.mbarrier.arrive.noinc), so
 //     producers never wait for their own copies.  Token slots are prefetched one tile ahead into a register and
 //     published to the other producer warps through a double-buffered shared-memory ring.
 //   * registers are re-balanced with setmaxnreg (consumers 208, producers 88).
-constexpr int kWsThreads = 384;
-constexpr int kWsProducers = 128;
-
-template <int D, int HB, int KVB, int NSTAGE>
-struct DecodeWsCfg : DecodeCfg<D, HB, KVB, NSTAGE> {
-  using Base = DecodeCfg<D, HB, KVB, NSTAGE>;
-  static constexpr int P_ITERS = Base::CHUNKS / kWsProducers;
-  static_assert(Base::CHUNKS % kWsProducers == 0, "tile must divide over the producer warps");
-  static constexpr int WS_REDB = (Base::TS > 1) ? (kDecodeWarps / 2) * Base::RED_ROWS * (D + 2) * 4 : 0;
-  static constexpr int WS_IDXB = 2 * Base::NT * 4;
-  static constexpr int WS_BARB = 2 * NSTAGE * 8;
-  static constexpr int OFF_RED = NSTAGE * Base::STAGEB;
-  static constexpr int OFF_IDX = OFF_RED + WS_REDB;
-  static constexpr int OFF_BAR = OFF_IDX + WS_IDXB;
-  static constexpr int WS_SMEM = OFF_BAR + WS_BARB + 128;
-};
-
 __device__ __forceinline__ void named_barrier(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE>
-__global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodeParams p) {
-  using Cfg = DecodeWsCfg<D, HB, KVB, NSTAGE>;
+__global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeParams p) {
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
   constexpr bool kFp8 = (KVB == 1);
   constexpr bool kMmaBf16 = kQBf16 && !kFp8;  // fp8 K/V are dequantised to f16 (exact)
   constexpr int TS = Cfg::TS, NT = Cfg::NT;
@@ -597,7 +142,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
     next_req_sh = first_req[cta];
     next_unit_sh = u_begin;
     for (int s = 0; s < NSTAGE; ++s) {
-      ptx::mbar_init(full_bar(s), kWsProducers);
+      ptx::mbar_init(full_bar(s), kProducerThreads);
       ptx::mbar_init(empty_bar(s), kDecodeWarps);
     }
     ptx::fence_mbar_init();
@@ -622,8 +167,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
       const uint8_t* kpool = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
       const uint8_t* vpool = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
       const int64_t pool_row_bytes = p.pool_tok_stride * KVB;
-      static_assert(Cfg::CPR <= kWsProducers && kWsProducers % Cfg::CPR == 0, "a token row must divide the producer threads");
-      constexpr int kTpi = kWsProducers / Cfg::CPR;  // tokens covered per iteration
+      static_assert(Cfg::CPR <= kProducerThreads && kProducerThreads % Cfg::CPR == 0, "a token row must divide the producer threads");
+      constexpr int kTpi = kProducerThreads / Cfg::CPR;  // tokens covered per iteration
       const int tok_lo = ptid / Cfg::CPR;
       const int cr = ptid % Cfg::CPR;
       const int ch = cr % Cfg::CPH;
@@ -643,7 +188,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
       };
       fetch();
       if (ptid < NT) idx_ring[ptid] = pend;
-      named_barrier(2, kWsProducers);
+      named_barrier(2, kProducerThreads);
       fetch();
       int cur = 0;
       for (int sg = 0; sg < n_segs; ++sg) {
@@ -667,7 +212,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
           ptx::cp_async_mbar_arrive_noinc(full_bar(stage));
           if (ptid < NT) idx_ring[(cur ^ 1) * NT + ptid] = pend;  // slots of the next tile (fetched a tile ago)
           fetch();
-          named_barrier(2, kWsProducers);
+          named_barrier(2, kProducerThreads);
           cur ^= 1;
           advance();
         }
@@ -678,28 +223,28 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
   } else {
     ptx::setmaxnreg_inc<208>();
     while (true) {
-    // ---------------- build the next batch of segments (thread 0), at most kMaxSeg
-    if (tid == 0) {
-      int i = next_req_sh, u = next_unit_sh, n = 0;
-      while (u < u_end && n < kMaxSeg) {
-        while (cum[i + 1] <= u) ++i;
-        const int c0 = cum[i], c1 = cum[i + 1];
-        const int seg_end = min(c1, u_end);
-        const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
-        Segment s;
-        s.batch = i;
-        s.tok_begin = (u - c0) * kUnit;
-        s.tok_end = min((seg_end - c0) * kUnit, L);
-        const bool is_first = (u == c0), is_last = (seg_end == c1);
-        s.slot = (is_first && is_last) ? -1 : (is_first ? 2 * cta + 1 : 2 * cta);
-        s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride;
-        segs[n++] = s;
-        u = seg_end;
+      // ---------------- build the next batch of segments (thread 0), at most kMaxSeg
+      if (tid == 0) {
+        int i = next_req_sh, u = next_unit_sh, n = 0;
+        while (u < u_end && n < kMaxSeg) {
+          while (cum[i + 1] <= u) ++i;
+          const int c0 = cum[i], c1 = cum[i + 1];
+          const int seg_end = min(c1, u_end);
+          const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
+          Segment s;
+          s.batch = i;
+          s.tok_begin = (u - c0) * kUnit;
+          s.tok_end = min((seg_end - c0) * kUnit, L);
+          const bool is_first = (u == c0), is_last = (seg_end == c1);
+          s.slot = (is_first && is_last) ? -1 : (is_first ? 2 * cta + 1 : 2 * cta);
+          s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride;
+          segs[n++] = s;
+          u = seg_end;
+        }
+        n_segs_sh = n;
+        next_req_sh = i;
+        next_unit_sh = u;
       }
-      n_segs_sh = n;
-      next_req_sh = i;
-      next_unit_sh = u;
-    }
       __syncthreads();
       const int n_segs = n_segs_sh;
       if (n_segs == 0) break;
@@ -714,289 +259,289 @@ __global__ void __launch_bounds__(kWsThreads, 1) decode_ws_kernel(const DecodePa
         const Segment seg = segs[sg];
         const int ntiles = (seg.tok_end - seg.tok_begin + NT - 1) / NT;
 
-      // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
-      uint32_t qa[KSTEPS][4];
-      {
-        const uint16_t* qrow0 = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride +
-                                static_cast<int64_t>(kv_head * G + row) * D;
-        const uint16_t* qrow1 = qrow0 + 8 * D;
-        const bool v0 = row < G, v1 = !kG8 && (row + 8 < G);
-#pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks) {
-          uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-          if constexpr (!kFp8) {
-            if (v0) {
-              a0 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 2 * qd);
-              a2 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 8 + 2 * qd);
-            }
-            if (v1) {
-              a1 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 2 * qd);
-              a3 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 8 + 2 * qd);
-            }
-          } else {
-            // fp8 K: a thread's ldmatrix register holds d = 16*ks + 4*qd + {0,1,2,3}; the
-            // contraction index is permuted identically on the Q side.
-            if (v0) {
-              const uint2 t = *reinterpret_cast<const uint2*>(qrow0 + ks * 16 + 4 * qd);
-              a0 = t.x; a2 = t.y;
-            }
-            if (v1) {
-              const uint2 t = *reinterpret_cast<const uint2*>(qrow1 + ks * 16 + 4 * qd);
-              a1 = t.x; a3 = t.y;
-            }
-            if constexpr (kQBf16) {  // bf16 -> f16 (saturating), the MMA runs in f16 for fp8 KV
-              auto cv = [](uint32_t x) {
-                const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
-                const float l2 = fminf(fmaxf(lo, -65504.f), 65504.f), h2 = fminf(fmaxf(hi, -65504.f), 65504.f);
-                return pack2<false>(l2, h2);
-              };
-              a0 = cv(a0); a1 = cv(a1); a2 = cv(a2); a3 = cv(a3);
-            }
-          }
-          qa[ks][0] = a0; qa[ks][1] = a1; qa[ks][2] = a2; qa[ks][3] = a3;
-        }
-      }
-
-      float o[NBLK][4];
-#pragma unroll
-      for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
-      float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-
-      for (int t = 0; t < ntiles; ++t) {
-        ptx::mbar_wait(full_bar(stage), phase);
-        const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
-        const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
-        const uint32_t k_s = smem_u32(stage_base + stage * Cfg::STAGEB);
-        const uint32_t v_s = k_s + Cfg::TILEB;
-        if (nvalid > 0) {
-        // ---- S = Q K^T for 16 tokens (2 n-blocks of 8)
-        float s[2][4];
-#pragma unroll
-        for (int nb = 0; nb < 2; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
-        if constexpr (!kFp8) {
-#pragma unroll
+        // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
+        uint32_t qa[KSTEPS][4];
+        {
+          const uint16_t* qrow0 = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride +
+                                  static_cast<int64_t>(kv_head * G + row) * D;
+          const uint16_t* qrow1 = qrow0 + 8 * D;
+          const bool v0 = row < G, v1 = !kG8 && (row + 8 < G);
+  #pragma unroll
           for (int ks = 0; ks < KSTEPS; ++ks) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj >> 1) * 8 + mr;
-            const int ch = 2 * ks + (mj & 1);
-            uint32_t r[4];
-            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-            mma_16816<kMmaBf16>(s[0], qa[ks], r[0], r[1]);
-            mma_16816<kMmaBf16>(s[1], qa[ks], r[2], r[3]);
-          }
-        } else {
-          // fp8: one 16-byte chunk = 16 d; matrices (tok 0-7, ch), (tok 8-15, ch), (tok 0-7, ch+1), (tok 8-15, ch+1)
-#pragma unroll
-          for (int kp = 0; kp < KSTEPS / 2; ++kp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * kp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const uint32_t r0 = r[2 * half], r1 = r[2 * half + 1];
-              const int ks = 2 * kp + half;
-              mma_16816<false>(s[0], qa[ks], e4m3x2_to_f16x2(r0 & 0xffff), e4m3x2_to_f16x2(r0 >> 16));
-              mma_16816<false>(s[1], qa[ks], e4m3x2_to_f16x2(r1 & 0xffff), e4m3x2_to_f16x2(r1 >> 16));
-            }
-          }
-        }
-
-        // ---- scale, cap, mask, online softmax (log2 domain)
-#pragma unroll
-        for (int nb = 0; nb < 2; ++nb) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x;
-            if (p.logit_cap > 0.f) {
-              x = p.logit_cap * fast_tanh(s[nb][e] * p.scale_raw / p.logit_cap) * kLog2e;
-            } else {
-              x = s[nb][e] * p.scale_log2;
-            }
-            const int col = nb * 8 + 2 * qd + (e & 1);
-            s[nb][e] = (col < nvalid) ? x : -INFINITY;
-          }
-        }
-        float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        const float mn0 = fmaxf(m0, mx0);  // finite: at least one valid column
-        const float al0 = fast_exp2(m0 - mn0);
-        m0 = mn0;
-        float p00 = fast_exp2(s[0][0] - mn0), p01 = fast_exp2(s[0][1] - mn0);
-        float p10 = fast_exp2(s[1][0] - mn0), p11 = fast_exp2(s[1][1] - mn0);
-        l0 = l0 * al0 + (p00 + p01 + p10 + p11);
-        uint32_t pa[4];
-        pa[0] = pack2<kMmaBf16>(p00, p01);
-        pa[2] = pack2<kMmaBf16>(p10, p11);
-        float al1 = 1.f;
-        if constexpr (!kG8) {
-          float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
-          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-          const float mn1 = fmaxf(m1, mx1);
-          al1 = fast_exp2(m1 - mn1);
-          m1 = mn1;
-          const float q00 = fast_exp2(s[0][2] - mn1), q01 = fast_exp2(s[0][3] - mn1);
-          const float q10 = fast_exp2(s[1][2] - mn1), q11 = fast_exp2(s[1][3] - mn1);
-          l1 = l1 * al1 + (q00 + q01 + q10 + q11);
-          pa[1] = pack2<kMmaBf16>(q00, q01);
-          pa[3] = pack2<kMmaBf16>(q10, q11);
-        } else {
-          pa[1] = 0u; pa[3] = 0u;
-        }
-#pragma unroll
-        for (int nb = 0; nb < NBLK; ++nb) {
-          o[nb][0] *= al0; o[nb][1] *= al0;
-          if constexpr (!kG8) { o[nb][2] *= al1; o[nb][3] *= al1; }
-        }
-
-        // ---- O += P V
-        if constexpr (!kFp8) {
-#pragma unroll
-          for (int jp = 0; jp < NBLK / 2; ++jp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * jp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-            mma_16816<kMmaBf16>(o[2 * jp], pa, r[0], r[1]);
-            mma_16816<kMmaBf16>(o[2 * jp + 1], pa, r[2], r[3]);
-          }
-        } else {
-          // fp8 V: a transposed b16 ldmatrix hands a thread (tok 2qd, d pair), (tok 2qd+1, d pair);
-          // regroup bytes so each half-word is one d for two consecutive tokens.
-          // chunk c (16 d) -> n-block "even d" o[4c'+..]; accumulator column order is fixed up at the store.
-#pragma unroll
-          for (int cp = 0; cp < D / 32; ++cp) {
-            const int mj = lane >> 3, mr = lane & 7;
-            const int tok = ts * 16 + (mj & 1) * 8 + mr;
-            const int ch = 2 * cp + (mj >> 1);
-            uint32_t r[4];
-            ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const uint32_t lo = r[2 * half], hi = r[2 * half + 1];  // tokens 0-7, tokens 8-15
-              const uint32_t e_lo = __byte_perm(lo, 0, 0x0020), o_lo = __byte_perm(lo, 0, 0x0031);
-              const uint32_t e_hi = __byte_perm(hi, 0, 0x0020), o_hi = __byte_perm(hi, 0, 0x0031);
-              const int c = 2 * cp + half;  // 16-d chunk
-              mma_16816<false>(o[2 * c], pa, e4m3x2_to_f16x2(e_lo), e4m3x2_to_f16x2(e_hi));
-              mma_16816<false>(o[2 * c + 1], pa, e4m3x2_to_f16x2(o_lo), e4m3x2_to_f16x2(o_hi));
-            }
-          }
-        }
-        }
-        // every ldmatrix of this tile has returned (the MMAs above consumed them): hand the stage back
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(empty_bar(stage));
-        advance();
-      }  // tiles
-
-      // ---- finish the piece: reduce l over the quad, merge the TS warps of a head, store
-      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-      if constexpr (!kG8) {
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-      }
-      if constexpr (TS > 1) {
-        // tree merge: in each round the upper half of the token sub-tiles hands its state to the lower half
-        constexpr int RSTRIDE = D + 2;
-                float* red = red_buf;  // dedicated: the producers refill stages asynchronously
-#pragma unroll
-        for (int half = TS / 2; half >= 1; half >>= 1) {
-          consumer_barrier();
-          if (ts >= half && ts < 2 * half) {
-            float* dst = red + ((ts - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
-#pragma unroll
-            for (int nb = 0; nb < NBLK; ++nb) {
-              *reinterpret_cast<float2*>(dst + row * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][0], o[nb][1]);
-              if constexpr (!kG8)
-                *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][2], o[nb][3]);
-            }
-            if (qd == 0) {
-              *reinterpret_cast<float2*>(dst + row * RSTRIDE + D) = make_float2(m0, l0);
-              if constexpr (!kG8) *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + D) = make_float2(m1, l1);
-            }
-          }
-          consumer_barrier();
-          if (ts < half) {
-            const float* src = red + (ts * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
-            {
-              const float2 ml = *reinterpret_cast<const float2*>(src + row * RSTRIDE + D);
-              const float mn = fmaxf(m0, ml.x);
-              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m0 - mn);
-              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
-              m0 = mn; l0 = l0 * a + ml.y * b;
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb) {
-                const float2 x = *reinterpret_cast<const float2*>(src + row * RSTRIDE + nb * 8 + 2 * qd);
-                o[nb][0] = o[nb][0] * a + x.x * b;
-                o[nb][1] = o[nb][1] * a + x.y * b;
-              }
-            }
-            if constexpr (!kG8) {
-              const float2 ml = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + D);
-              const float mn = fmaxf(m1, ml.x);
-              const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m1 - mn);
-              const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
-              m1 = mn; l1 = l1 * a + ml.y * b;
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb) {
-                const float2 x = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + nb * 8 + 2 * qd);
-                o[nb][2] = o[nb][2] * a + x.x * b;
-                o[nb][3] = o[nb][3] * a + x.y * b;
-              }
-            }
-          }
-        }
-      }
-
-      if (ts == 0) {
-#pragma unroll
-        for (int rr = 0; rr < (kG8 ? 1 : 2); ++rr) {
-          const int r = row + rr * 8;
-          if (r >= G) continue;
-          const float m = rr ? m1 : m0, l = rr ? l1 : l0;
-          const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
-          const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
-          const int head = kv_head * G + r;
-          if (seg.slot < 0) {
-            uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
-                            static_cast<int64_t>(head) * D;
+            uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
             if constexpr (!kFp8) {
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb)
-                *reinterpret_cast<uint32_t*>(dst + nb * 8 + 2 * qd) =
-                    pack2<kQBf16>(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
+              if (v0) {
+                a0 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 2 * qd);
+                a2 = *reinterpret_cast<const uint32_t*>(qrow0 + ks * 16 + 8 + 2 * qd);
+              }
+              if (v1) {
+                a1 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 2 * qd);
+                a3 = *reinterpret_cast<const uint32_t*>(qrow1 + ks * 16 + 8 + 2 * qd);
+              }
             } else {
-#pragma unroll
-              for (int c = 0; c < D / 16; ++c) {  // thread holds d = 16c + 4qd + {0,2} (even blk), {1,3} (odd blk)
-                const uint32_t w0 = pack2<kQBf16>(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv);
-                const uint32_t w1 = pack2<kQBf16>(o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
-                *reinterpret_cast<uint2*>(dst + c * 16 + 4 * qd) = make_uint2(w0, w1);
+              // fp8 K: a thread's ldmatrix register holds d = 16*ks + 4*qd + {0,1,2,3}; the
+              // contraction index is permuted identically on the Q side.
+              if (v0) {
+                const uint2 t = *reinterpret_cast<const uint2*>(qrow0 + ks * 16 + 4 * qd);
+                a0 = t.x; a2 = t.y;
+              }
+              if (v1) {
+                const uint2 t = *reinterpret_cast<const uint2*>(qrow1 + ks * 16 + 4 * qd);
+                a1 = t.x; a3 = t.y;
+              }
+              if constexpr (kQBf16) {  // bf16 -> f16 (saturating), the MMA runs in f16 for fp8 KV
+                auto cv = [](uint32_t x) {
+                  const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
+                  const float l2 = fminf(fmaxf(lo, -65504.f), 65504.f), h2 = fminf(fmaxf(hi, -65504.f), 65504.f);
+                  return pack2<false>(l2, h2);
+                };
+                a0 = cv(a0); a1 = cv(a1); a2 = cv(a2); a3 = cv(a3);
               }
             }
-            if (p.lse_out != nullptr && qd == 0) p.lse_out[static_cast<int64_t>(seg.batch) * p.Hq + head] = lse;
+            qa[ks][0] = a0; qa[ks][1] = a1; qa[ks][2] = a2; qa[ks][3] = a3;
+          }
+        }
+
+        float o[NBLK][4];
+  #pragma unroll
+        for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
+        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+        for (int t = 0; t < ntiles; ++t) {
+          ptx::mbar_wait(full_bar(stage), phase);
+          const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
+          const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
+          const uint32_t k_s = smem_u32(stage_base + stage * Cfg::STAGEB);
+          const uint32_t v_s = k_s + Cfg::TILEB;
+          if (nvalid > 0) {
+          // ---- S = Q K^T for 16 tokens (2 n-blocks of 8)
+          float s[2][4];
+  #pragma unroll
+          for (int nb = 0; nb < 2; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+          if constexpr (!kFp8) {
+  #pragma unroll
+            for (int ks = 0; ks < KSTEPS; ++ks) {
+              const int mj = lane >> 3, mr = lane & 7;
+              const int tok = ts * 16 + (mj >> 1) * 8 + mr;
+              const int ch = 2 * ks + (mj & 1);
+              uint32_t r[4];
+              ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              mma_16816<kMmaBf16>(s[0], qa[ks], r[0], r[1]);
+              mma_16816<kMmaBf16>(s[1], qa[ks], r[2], r[3]);
+            }
           } else {
-            float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D;
-            if constexpr (!kFp8) {
-#pragma unroll
-              for (int nb = 0; nb < NBLK; ++nb)
-                *reinterpret_cast<float2*>(dst + nb * 8 + 2 * qd) =
-                    make_float2(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
-            } else {
-#pragma unroll
-              for (int c = 0; c < D / 16; ++c)
-                *reinterpret_cast<float4*>(dst + c * 16 + 4 * qd) =
-                    make_float4(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv,
-                                o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
+            // fp8: one 16-byte chunk = 16 d; matrices (tok 0-7, ch), (tok 8-15, ch), (tok 0-7, ch+1), (tok 8-15, ch+1)
+  #pragma unroll
+            for (int kp = 0; kp < KSTEPS / 2; ++kp) {
+              const int mj = lane >> 3, mr = lane & 7;
+              const int tok = ts * 16 + (mj & 1) * 8 + mr;
+              const int ch = 2 * kp + (mj >> 1);
+              uint32_t r[4];
+              ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+  #pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                const uint32_t r0 = r[2 * half], r1 = r[2 * half + 1];
+                const int ks = 2 * kp + half;
+                mma_16816<false>(s[0], qa[ks], e4m3x2_to_f16x2(r0 & 0xffff), e4m3x2_to_f16x2(r0 >> 16));
+                mma_16816<false>(s[1], qa[ks], e4m3x2_to_f16x2(r1 & 0xffff), e4m3x2_to_f16x2(r1 >> 16));
+              }
             }
-            if (qd == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
+          }
+
+          // ---- scale, cap, mask, online softmax (log2 domain)
+  #pragma unroll
+          for (int nb = 0; nb < 2; ++nb) {
+  #pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float x;
+              if (p.logit_cap > 0.f) {
+                x = p.logit_cap * fast_tanh(s[nb][e] * p.scale_raw / p.logit_cap) * kLog2e;
+              } else {
+                x = s[nb][e] * p.scale_log2;
+              }
+              const int col = nb * 8 + 2 * qd + (e & 1);
+              s[nb][e] = (col < nvalid) ? x : -INFINITY;
+            }
+          }
+          float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+          mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+          mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+          const float mn0 = fmaxf(m0, mx0);  // finite: at least one valid column
+          const float al0 = fast_exp2(m0 - mn0);
+          m0 = mn0;
+          float p00 = fast_exp2(s[0][0] - mn0), p01 = fast_exp2(s[0][1] - mn0);
+          float p10 = fast_exp2(s[1][0] - mn0), p11 = fast_exp2(s[1][1] - mn0);
+          l0 = l0 * al0 + (p00 + p01 + p10 + p11);
+          uint32_t pa[4];
+          pa[0] = pack2<kMmaBf16>(p00, p01);
+          pa[2] = pack2<kMmaBf16>(p10, p11);
+          float al1 = 1.f;
+          if constexpr (!kG8) {
+            float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            const float mn1 = fmaxf(m1, mx1);
+            al1 = fast_exp2(m1 - mn1);
+            m1 = mn1;
+            const float q00 = fast_exp2(s[0][2] - mn1), q01 = fast_exp2(s[0][3] - mn1);
+            const float q10 = fast_exp2(s[1][2] - mn1), q11 = fast_exp2(s[1][3] - mn1);
+            l1 = l1 * al1 + (q00 + q01 + q10 + q11);
+            pa[1] = pack2<kMmaBf16>(q00, q01);
+            pa[3] = pack2<kMmaBf16>(q10, q11);
+          } else {
+            pa[1] = 0u; pa[3] = 0u;
+          }
+  #pragma unroll
+          for (int nb = 0; nb < NBLK; ++nb) {
+            o[nb][0] *= al0; o[nb][1] *= al0;
+            if constexpr (!kG8) { o[nb][2] *= al1; o[nb][3] *= al1; }
+          }
+
+          // ---- O += P V
+          if constexpr (!kFp8) {
+  #pragma unroll
+            for (int jp = 0; jp < NBLK / 2; ++jp) {
+              const int mj = lane >> 3, mr = lane & 7;
+              const int tok = ts * 16 + (mj & 1) * 8 + mr;
+              const int ch = 2 * jp + (mj >> 1);
+              uint32_t r[4];
+              ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              mma_16816<kMmaBf16>(o[2 * jp], pa, r[0], r[1]);
+              mma_16816<kMmaBf16>(o[2 * jp + 1], pa, r[2], r[3]);
+            }
+          } else {
+            // fp8 V: a transposed b16 ldmatrix hands a thread (tok 2qd, d pair), (tok 2qd+1, d pair);
+            // regroup bytes so each half-word is one d for two consecutive tokens.
+            // chunk c (16 d) -> n-block "even d" o[4c'+..]; accumulator column order is fixed up at the store.
+  #pragma unroll
+            for (int cp = 0; cp < D / 32; ++cp) {
+              const int mj = lane >> 3, mr = lane & 7;
+              const int tok = ts * 16 + (mj & 1) * 8 + mr;
+              const int ch = 2 * cp + (mj >> 1);
+              uint32_t r[4];
+              ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+  #pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                const uint32_t lo = r[2 * half], hi = r[2 * half + 1];  // tokens 0-7, tokens 8-15
+                const uint32_t e_lo = __byte_perm(lo, 0, 0x0020), o_lo = __byte_perm(lo, 0, 0x0031);
+                const uint32_t e_hi = __byte_perm(hi, 0, 0x0020), o_hi = __byte_perm(hi, 0, 0x0031);
+                const int c = 2 * cp + half;  // 16-d chunk
+                mma_16816<false>(o[2 * c], pa, e4m3x2_to_f16x2(e_lo), e4m3x2_to_f16x2(e_hi));
+                mma_16816<false>(o[2 * c + 1], pa, e4m3x2_to_f16x2(o_lo), e4m3x2_to_f16x2(o_hi));
+              }
+            }
+          }
+          }
+          // every ldmatrix of this tile has returned (the MMAs above consumed them): hand the stage back
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(empty_bar(stage));
+          advance();
+        }  // tiles
+
+        // ---- finish the piece: reduce l over the quad, merge the TS warps of a head, store
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        if constexpr (!kG8) {
+          l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+          l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        }
+        if constexpr (TS > 1) {
+          // tree merge: in each round the upper half of the token sub-tiles hands its state to the lower half
+          constexpr int RSTRIDE = D + 2;
+                  float* red = red_buf;  // dedicated: the producers refill stages asynchronously
+  #pragma unroll
+          for (int half = TS / 2; half >= 1; half >>= 1) {
+            consumer_barrier();
+            if (ts >= half && ts < 2 * half) {
+              float* dst = red + ((ts - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+  #pragma unroll
+              for (int nb = 0; nb < NBLK; ++nb) {
+                *reinterpret_cast<float2*>(dst + row * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][0], o[nb][1]);
+                if constexpr (!kG8)
+                  *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][2], o[nb][3]);
+              }
+              if (qd == 0) {
+                *reinterpret_cast<float2*>(dst + row * RSTRIDE + D) = make_float2(m0, l0);
+                if constexpr (!kG8) *reinterpret_cast<float2*>(dst + (row + 8) * RSTRIDE + D) = make_float2(m1, l1);
+              }
+            }
+            consumer_barrier();
+            if (ts < half) {
+              const float* src = red + (ts * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+              {
+                const float2 ml = *reinterpret_cast<const float2*>(src + row * RSTRIDE + D);
+                const float mn = fmaxf(m0, ml.x);
+                const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m0 - mn);
+                const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
+                m0 = mn; l0 = l0 * a + ml.y * b;
+  #pragma unroll
+                for (int nb = 0; nb < NBLK; ++nb) {
+                  const float2 x = *reinterpret_cast<const float2*>(src + row * RSTRIDE + nb * 8 + 2 * qd);
+                  o[nb][0] = o[nb][0] * a + x.x * b;
+                  o[nb][1] = o[nb][1] * a + x.y * b;
+                }
+              }
+              if constexpr (!kG8) {
+                const float2 ml = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + D);
+                const float mn = fmaxf(m1, ml.x);
+                const float a = (mn == -INFINITY) ? 0.f : fast_exp2(m1 - mn);
+                const float b = (mn == -INFINITY) ? 0.f : fast_exp2(ml.x - mn);
+                m1 = mn; l1 = l1 * a + ml.y * b;
+  #pragma unroll
+                for (int nb = 0; nb < NBLK; ++nb) {
+                  const float2 x = *reinterpret_cast<const float2*>(src + (row + 8) * RSTRIDE + nb * 8 + 2 * qd);
+                  o[nb][2] = o[nb][2] * a + x.x * b;
+                  o[nb][3] = o[nb][3] * a + x.y * b;
+                }
+              }
+            }
           }
         }
-      }
+
+        if (ts == 0) {
+  #pragma unroll
+          for (int rr = 0; rr < (kG8 ? 1 : 2); ++rr) {
+            const int r = row + rr * 8;
+            if (r >= G) continue;
+            const float m = rr ? m1 : m0, l = rr ? l1 : l0;
+            const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
+            const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+            const int head = kv_head * G + r;
+            if (seg.slot < 0) {
+              uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
+                              static_cast<int64_t>(head) * D;
+              if constexpr (!kFp8) {
+  #pragma unroll
+                for (int nb = 0; nb < NBLK; ++nb)
+                  *reinterpret_cast<uint32_t*>(dst + nb * 8 + 2 * qd) =
+                      pack2<kQBf16>(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
+              } else {
+  #pragma unroll
+                for (int c = 0; c < D / 16; ++c) {  // thread holds d = 16c + 4qd + {0,2} (even blk), {1,3} (odd blk)
+                  const uint32_t w0 = pack2<kQBf16>(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv);
+                  const uint32_t w1 = pack2<kQBf16>(o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
+                  *reinterpret_cast<uint2*>(dst + c * 16 + 4 * qd) = make_uint2(w0, w1);
+                }
+              }
+              if (p.lse_out != nullptr && qd == 0) p.lse_out[static_cast<int64_t>(seg.batch) * p.Hq + head] = lse;
+            } else {
+              float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D;
+              if constexpr (!kFp8) {
+  #pragma unroll
+                for (int nb = 0; nb < NBLK; ++nb)
+                  *reinterpret_cast<float2*>(dst + nb * 8 + 2 * qd) =
+                      make_float2(o[nb][2 * rr] * inv, o[nb][2 * rr + 1] * inv);
+              } else {
+  #pragma unroll
+                for (int c = 0; c < D / 16; ++c)
+                  *reinterpret_cast<float4*>(dst + c * 16 + 4 * qd) =
+                      make_float4(o[2 * c][2 * rr] * inv, o[2 * c + 1][2 * rr] * inv,
+                                  o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
+              }
+              if (qd == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
+            }
+          }
+        }
       }  // segments
       __syncthreads();  // every role is done with the segment list
     }
@@ -1061,10 +606,8 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
 // ---------------------------------------------------------------------------------------
 template <int D, int HB, int KVB, bool kQBf16, bool kG8>
 static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
-  // ~192 KiB of staging per SM: 3 stages of 64 KiB (D=128 bf16) or 6 stages of 32/16 KiB; one stage less
-  // when the cross-warp merge buffer cannot alias a stage and the total would pass the 227 KiB CTA limit
   constexpr int kWant = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
-  constexpr int kStatic = 2048;  // static __shared__ (segment list, cursors) + the 1 KiB the driver reserves
+  constexpr int kStatic = 2048;
   constexpr int NSTAGE = (DecodeCfg<D, HB, KVB, kWant>::SMEM + kStatic <= 227 * 1024) ? kWant : kWant - 1;
   using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
   static_assert(Cfg::SMEM + kStatic <= 227 * 1024, "decode staging exceeds the shared memory of one CTA");
@@ -1080,35 +623,8 @@ static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st
   return B200ATTN_OK;
 }
 
-template <int D, int HB, int KVB, bool kQBf16, bool kG8>
-static int launch_decode_ws(const DecodeParams& p, int head_groups, cudaStream_t st) {
-  constexpr int kWant = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
-  constexpr int kStatic = 2048;
-  constexpr int NSTAGE = (DecodeWsCfg<D, HB, KVB, kWant>::WS_SMEM + kStatic <= 227 * 1024) ? kWant : kWant - 1;
-  using Cfg = DecodeWsCfg<D, HB, KVB, NSTAGE>;
-  static_assert(Cfg::WS_SMEM + kStatic <= 227 * 1024, "decode staging exceeds the shared memory of one CTA");
-  auto kern = decode_ws_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::WS_SMEM));
-    configured = true;
-  }
-  dim3 grid(p.n_ctas, head_groups, 1);
-  kern<<<grid, kWsThreads, Cfg::WS_SMEM, st>>>(p);
-  B2_CUDA(cudaGetLastError());
-  return B200ATTN_OK;
-}
-
 template <int D, int KVB, bool kQBf16, bool kG8>
 static int dispatch_hb(const DecodeParams& p, int Hkv, cudaStream_t st) {
-  // B200ATTN_DECODE_IMPL=mono selects the monolithic kernel (dev knob for A/B timing)
-  static const bool ws = [] { const char* e = getenv("B200ATTN_DECODE_IMPL"); return !(e && e[0] == 'm'); }();
-  if (ws) {
-    if (Hkv % 8 == 0) return launch_decode_ws<D, 8, KVB, kQBf16, kG8>(p, Hkv / 8, st);
-    if (Hkv % 4 == 0) return launch_decode_ws<D, 4, KVB, kQBf16, kG8>(p, Hkv / 4, st);
-    if (Hkv % 2 == 0) return launch_decode_ws<D, 2, KVB, kQBf16, kG8>(p, Hkv / 2, st);
-    return launch_decode_ws<D, 1, KVB, kQBf16, kG8>(p, Hkv, st);
-  }
   if (Hkv % 8 == 0) return launch_decode<D, 8, KVB, kQBf16, kG8>(p, Hkv / 8, st);
   if (Hkv % 4 == 0) return launch_decode<D, 4, KVB, kQBf16, kG8>(p, Hkv / 4, st);
   if (Hkv % 2 == 0) return launch_decode<D, 2, KVB, kQBf16, kG8>(p, Hkv / 2, st);
