@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_VERSION 100 /* 0.1.0 */
+#define B200ATTN_VERSION 101 /* 0.1.1 */
 
 /* element types */
 #define B200ATTN_BF16 0
@@ -96,6 +96,30 @@ int b200attn_kv_write(const void* k, const void* v, int64_t k_tok_stride, int64_
                       int pool_dtype, float k_scale_host, float v_scale_host, const float* k_scale_dev,
                       const float* v_scale_dev, int n_scales, int scale_mode, int writeback_scaled,
                       b200attn_stream_t stream);
+
+/* ---------------------------------------------------------------- fused rotary embedding + KV write
+ * The two steps the reference runs right before attention, in one launch:
+ *   q, k = rotary_emb(positions, q, k)      layers/rotary_embedding.py:138-166 (forward_native), :218-244 (forward_cuda ->
+ *                                           sgl-kernel apply_rope_with_cos_sin_cache_inplace, csrc/elementwise/rope.cu:22-89)
+ *   set_kv_buffer(layer, loc, k, v)         mem_cache/memory_pool.py:420-458
+ * q [T,Hq,D] and k [T,Hkv,D] are rotated IN PLACE (head stride D, token strides given); the rotated k and v are cast
+ * and scattered into the pool with exactly the rules of b200attn_kv_write.  loc == NULL: rotate only, no pool write.
+ *   positions      [T] int64 or int32
+ *   cos_sin_cache  [max_position, rotary_dim] = cos | sin halves (rotary_embedding.py:125-136); fp32 (what the
+ *                  reference keeps on CUDA) or the tensor dtype (what it keeps on CPU, :101-102)
+ *   is_neox        != 0: x1 | x2 are the two halves of the rotary part; 0: GPT-J even / odd interleave (:57-67)
+ *   math_mode      ROPE_FP32: fp32 products, one rounding (the CUDA op); ROPE_NATIVE: forward_native's op-by-op
+ *                  rounding in the tensor dtype -- bit-exact with the reference's CPU path
+ * D and rotary_dim must be multiples of 16. */
+#define B200ATTN_ROPE_FP32 0
+#define B200ATTN_ROPE_NATIVE 1
+int b200attn_rope_kv_write(void* q, int64_t q_tok_stride, void* k, int64_t k_tok_stride, const void* v,
+                           int64_t v_tok_stride, const void* positions, int pos_is_i64,
+                           const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox, int T,
+                           int Hq, int Hkv, int D, int dtype, const int64_t* loc, void* k_pool, void* v_pool,
+                           int64_t pool_tok_stride, int pool_dtype, float k_scale_host, float v_scale_host,
+                           const float* k_scale_dev, const float* v_scale_dev, int n_scales, int scale_mode,
+                           int math_mode, b200attn_stream_t stream);
 
 /* ---------------------------------------------------------------- decode
  * Split-KV plan, computed on the device from seq_lens (no host sync, graph safe).

@@ -119,3 +119,24 @@ def ref_extend(q, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens, ex
                                         extend_prefix_lens, extend_seq_lens, scaling=scaling,
                                         enable_gqa=q.shape[1] != k_cache.shape[1], causal=causal)
     return out
+
+
+def ref_rotary_embedding(head_size: int, rotary_dim: int, max_position: int, base, is_neox: bool, dtype,
+                         rope_scaling=None):
+    """The reference's own rotary embedding module (layers/rotary_embedding.py, `get_rope` :1385-) built for the CPU:
+    its `forward_native(positions, query, key)` is what oracle/rope.py restates."""
+    import torch.nn as nn
+    load()
+    name = "sglang.srt.layers.rotary_embedding"
+    if name not in sys.modules or not hasattr(sys.modules[name], "get_rope"):
+        class CustomOp(nn.Module):  # sglang/srt/custom_op.py: dispatches forward() to a backend method
+            def forward(self, *a, **k):
+                return self.forward_native(*a, **k)
+        _stub("sglang.srt.custom_op", CustomOp=CustomOp)
+        _stub("sglang.srt.utils", cpu_has_amx_support=lambda: True, is_cpu=lambda: True, is_hip=lambda: False,
+              is_cuda=lambda: False, is_npu=lambda: False, get_bool_env_var=lambda *a, **k: False)
+        _load(name, os.path.join(_SRT, "layers", "rotary_embedding.py"))
+    mod = sys.modules[name]
+    if rope_scaling is None:
+        return mod.RotaryEmbedding(head_size, rotary_dim, max_position, base, is_neox, dtype)
+    return mod.get_rope(head_size, rotary_dim, max_position, base, is_neox, rope_scaling=dict(rope_scaling), dtype=dtype)

@@ -14,6 +14,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
 SCALE_DIV, SCALE_RCP = 0, 1
 EXTEND_AUTO, EXTEND_TCGEN05, EXTEND_MMA = 0, 1, 2
+ROPE_FP32, ROPE_NATIVE = 0, 1
 
 ERR_NAMES = {0: "OK", -1: "INVALID", -2: "UNSUPPORTED", -3: "CUDA", -4: "WORKSPACE"}
 
@@ -26,6 +27,8 @@ SIGNATURES = {
     "b200attn_device_info": (_i, [C.POINTER(_i)] * 4),
     "b200attn_kv_write": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _i, _i, _i, _vp, _vp, _i64, _i, _i,
                                _f, _f, _vp, _vp, _i, _i, _i, _vp]),
+    "b200attn_rope_kv_write": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp,
+                                    _vp, _vp, _i64, _i, _f, _f, _vp, _vp, _i, _i, _i, _vp]),
     "b200attn_decode_plan_bytes": (_sz, [_i, _i]),
     "b200attn_decode_plan": (_i, [_vp, _i, _i, _i, _i, _vp, _sz, _vp]),
     "b200attn_decode_workspace_bytes": (_sz, [_i, _i, _i]),

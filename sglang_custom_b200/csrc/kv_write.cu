@@ -5,6 +5,7 @@
 // of one (token, head) row, K and V handled by the same launch (blockIdx.y selects).
 // Algorithmic bytes per token: Hkv * D * (2 * in_size + 2 * pool_size) + 8 (loc).
 #include "common.cuh"
+#include "kv_quant.cuh"
 
 namespace b200attn {
 
@@ -22,23 +23,6 @@ struct KvWriteParams {
   int writeback;
   int T, Hkv, D;
 };
-
-template <bool kBf16>
-__device__ __forceinline__ float in_to_f32(uint16_t b) {
-  if constexpr (kBf16) {
-    return __uint_as_float(static_cast<uint32_t>(b) << 16);
-  } else {
-    return __half2float(__ushort_as_half(b));
-  }
-}
-template <bool kBf16>
-__device__ __forceinline__ uint16_t f32_to_in(float f) {
-  if constexpr (kBf16) {
-    return __bfloat16_as_ushort(__float2bfloat16_rn(f));
-  } else {
-    return __half_as_ushort(__float2half_rn(f));
-  }
-}
 
 // kMode 0: same-dtype bit copy. kMode 1: 16-bit float -> e4m3 with optional scale.
 template <bool kBf16, int kMode>
@@ -62,34 +46,10 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
     } else {
       float scale = p.scale_host[which];
       if (p.scale_dev[which] != nullptr) scale = p.scale_dev[which][p.n_scales > 1 ? h : 0];
-      const bool scaled = (scale != 0.0f);
-      const float inv = (p.scale_mode == B200ATTN_SCALE_RCP && scaled) ? __fdiv_rn(1.0f, scale) : 0.0f;
-      const uint32_t w[4] = {in.x, in.y, in.z, in.w};
-      uint32_t back[4];
-      uint32_t out8[2] = {0u, 0u};
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint16_t b = static_cast<uint16_t>(w[i >> 1] >> ((i & 1) * 16));
-        float f = in_to_f32<kBf16>(b);
-        uint16_t rb = b;
-        if (scaled) {
-          // torch: cache_k.div_(scale) happens in the tensor's own 16-bit dtype (rounded once here)
-          f = (p.scale_mode == B200ATTN_SCALE_RCP) ? __fmul_rn(f, inv) : __fdiv_rn(f, scale);
-          rb = f32_to_in<kBf16>(f);
-          f = in_to_f32<kBf16>(rb);
-        }
-        if (i & 1) {
-          back[i >> 1] |= static_cast<uint32_t>(rb) << 16;
-        } else {
-          back[i >> 1] = rb;
-        }
-        out8[i >> 2] |= static_cast<uint32_t>(f32_to_e4m3_torch(f)) << ((i & 3) * 8);
-      }
-      *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.pool[which]) + dst_elem) =
-          make_uint2(out8[0], out8[1]);
-      if (p.writeback && scaled) {
-        *reinterpret_cast<uint4*>(const_cast<uint16_t*>(s)) = make_uint4(back[0], back[1], back[2], back[3]);
-      }
+      uint4 back;
+      const uint2 q8 = quantize_chunk_e4m3<kBf16>(in, scale, p.scale_mode, back);
+      *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.pool[which]) + dst_elem) = q8;
+      if (p.writeback && scale != 0.0f) *reinterpret_cast<uint4*>(const_cast<uint16_t*>(s)) = back;
     }
   }
 }

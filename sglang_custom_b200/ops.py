@@ -116,6 +116,51 @@ def set_kv_buffer(k_buffer: torch.Tensor, v_buffer: torch.Tensor, loc: torch.Ten
              writeback_scaled)
 
 
+def rope_kv_write(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, cos_sin_cache: torch.Tensor,
+                  is_neox: bool, v: Optional[torch.Tensor] = None, loc: Optional[torch.Tensor] = None,
+                  k_pool: Optional[torch.Tensor] = None, v_pool: Optional[torch.Tensor] = None,
+                  k_scale: ScaleT = None, v_scale: ScaleT = None, pool_dtype: Optional[torch.dtype] = None,
+                  scale_mode: int = _lib.SCALE_DIV, math_mode: int = _lib.ROPE_FP32) -> None:
+    """In place: q, k = rotary_emb(positions, q, k) (layers/rotary_embedding.py:138-166 / :218-244) and, when `loc`
+    is given, set_kv_buffer(loc, k, v) (memory_pool.py:420-458) in the same launch.
+    q [T,Hq,D], k/v [T,Hkv,D] (views with head stride D); cos_sin_cache [max_pos, rotary_dim] fp32 or q.dtype."""
+    _cuda(positions, q, k, v, cos_sin_cache, loc, k_pool, v_pool)
+    if q.dim() != 3 or k.dim() != 3 or q.shape[0] != k.shape[0] or q.shape[2] != k.shape[2] or k.dtype != q.dtype:
+        raise B200AttnError(f"rope_kv_write: q [T,Hq,D] / k [T,Hkv,D] expected, got {tuple(q.shape)} {tuple(k.shape)}")
+    T, Hq, D = q.shape
+    Hkv = k.shape[1]
+    for name, t in (("q", q), ("k", k)) + ((("v", v),) if v is not None else ()):
+        if t.stride(2) != 1 or t.stride(1) != D:
+            raise B200AttnError(f"rope_kv_write: {name} must have strides (*, D, 1)")
+    if positions.numel() != T or not positions.is_contiguous():
+        raise B200AttnError("rope_kv_write: positions must be a contiguous [T] tensor")
+    if cos_sin_cache.dim() != 2 or not cos_sin_cache.is_contiguous():
+        raise B200AttnError("rope_kv_write: cos_sin_cache must be contiguous [max_position, rotary_dim]")
+    ks_h = vs_h = 0.0
+    ks_d = vs_d = None
+    n = 1
+    pool_dt = _dt(q.dtype)
+    if loc is not None:
+        if v is None or k_pool is None or v_pool is None or v.shape != k.shape:
+            raise B200AttnError("rope_kv_write: v, k_pool and v_pool are required with loc")
+        if loc.dtype != torch.int64 or loc.numel() != T or not loc.is_contiguous():
+            raise B200AttnError("rope_kv_write: loc must be a contiguous int64 [T] tensor")
+        if k_pool.dim() != 3 or k_pool.shape[1:] != (Hkv, D) or v_pool.shape != k_pool.shape or \
+                k_pool.stride(2) != 1 or k_pool.stride(1) != D:
+            raise B200AttnError("rope_kv_write: pool must be [P,Hkv,D] with strides (*, D, 1)")
+        pool_dt = _pool_dtype(k_pool, pool_dtype)
+        if pool_dt != _dt(q.dtype):
+            ks_h, ks_d, n1 = _scale_args(k_scale)
+            vs_h, vs_d, n2 = _scale_args(v_scale)
+            n = max(n1, n2)
+    check(_lib.load().b200attn_rope_kv_write(
+        q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), _ptr(v), v.stride(0) if v is not None else 0,
+        positions.data_ptr(), _is_i64(positions), cos_sin_cache.data_ptr(), _dt(cos_sin_cache.dtype),
+        cos_sin_cache.shape[1], int(bool(is_neox)), T, Hq, Hkv, D, _dt(q.dtype), _ptr(loc), _ptr(k_pool),
+        _ptr(v_pool), k_pool.stride(0) if k_pool is not None else 0, pool_dt, ks_h, vs_h, _ptr(ks_d), _ptr(vs_d), n,
+        int(scale_mode), int(math_mode), _stream(q)), "b200attn_rope_kv_write")
+
+
 def decode_plan_bytes(max_bs: int, n_ctas: int) -> int:
     return _lib.load().b200attn_decode_plan_bytes(int(max_bs), int(n_ctas))
 

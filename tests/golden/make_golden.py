@@ -83,8 +83,37 @@ def fp8_write_case(seed: int, scale) -> dict:
                 ref_v_pool_after=vp, ref_k_after_call=k_in, ref_v_after_call=v_in)
 
 
+LLAMA3_SCALING = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                  "original_max_position_embeddings": 8192}
+# name -> head_size, rotary_dim, max_position, base, is_neox, dtype, rope_scaling, Hq, Hkv, T
+ROPE_CASES = {
+    "rope_neox_llama3": (128, 128, 16384, 500000, True, torch.bfloat16, LLAMA3_SCALING, 8, 2, 19),
+    "rope_neox_d64": (64, 64, 2048, 10000, True, torch.bfloat16, None, 4, 4, 11),
+    "rope_gptj_partial": (128, 64, 2048, 10000, False, torch.bfloat16, None, 4, 1, 13),
+    "rope_neox_f16": (128, 128, 4096, 10000, True, torch.float16, None, 2, 2, 7),
+}
+
+
+def rope_case(seed: int, hs, rd, max_pos, base, neox, dtype, scaling, Hq, Hkv, T) -> dict:
+    """The reference's RotaryEmbedding.forward_native (layers/rotary_embedding.py:138-166) on random q/k, with the
+    table the reference module itself built (in `dtype`, as it keeps it off CUDA, :101-102)."""
+    g = torch.Generator().manual_seed(seed)
+    ref = ref_loader.ref_rotary_embedding(hs, rd, max_pos, base, neox, dtype, scaling)
+    q = torch.randn((T, Hq * hs), generator=g).to(dtype)
+    k = torch.randn((T, Hkv * hs), generator=g).to(dtype)
+    pos = torch.randint(0, max_pos, (T,), generator=g)
+    pos[0], pos[-1] = 0, max_pos - 1
+    rq, rk = ref.forward_native(pos, q.clone(), k.clone())
+    return dict(head_size=hs, rotary_dim=rd, max_position=max_pos, base=float(base), is_neox=bool(neox),
+                dtype_name=str(dtype).replace("torch.", ""), llama3=scaling is not None, Hq=Hq, Hkv=Hkv,
+                q=q, k=k, positions=pos, ref_cache_rows=ref.cos_sin_cache.index_select(0, pos), ref_q=rq, ref_k=rk)
+
+
 def main() -> None:
     torch.set_num_threads(1)
+    for i, (name, args) in enumerate(ROPE_CASES.items()):
+        torch.save(rope_case(401 + i, *args), OUT / f"{name}.pt")
+        print("wrote", name)
     for name, kw in CASES.items():
         torch.save(run_case(kw), OUT / f"{name}.pt")
         print("wrote", name)

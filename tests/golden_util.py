@@ -8,7 +8,8 @@ import torch
 
 GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 
-ATTN_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("*.pt") if not p.stem.startswith("kvwrite"))
+ATTN_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("*.pt") if not p.stem.startswith(("kvwrite", "rope")))
+ROPE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("rope*.pt"))
 KVWRITE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("kvwrite*.pt"))
 
 
