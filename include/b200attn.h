@@ -222,6 +222,29 @@ int b200attn_flatten_kv_indices(const int32_t* req_to_token, int64_t table_strid
 int b200attn_gather_kv(const void* pool, int64_t pool_tok_stride_bytes, const int32_t* indices,
                        int64_t n, int64_t row_bytes, void* dst, b200attn_stream_t stream);
 
+/* ---------------------------------------------------------------- HiCache KV page transfer
+ * Copies n_items items of item_bytes bytes between two KV pools, for layers [start_layer, start_layer + num_layers):
+ *     dst(layer, dst_indices[i]) = src(layer, src_indices[i])        for K and (when src_v != NULL) V
+ * Replaces sgl-kernel/csrc/kvcacheio/transfer.cu:61-430 (transfer_kv_per_layer, _per_layer_pf_lf, _all_layer,
+ * _all_layer_lf_pf and their _mla forms -- pass src_v = dst_v = NULL for the single-buffer MLA forms).
+ * Either side may be pinned (mapped) host memory: the kernel then reads / writes it directly over the host link.
+ * Layouts (how the address of (layer, index) is formed, transfer.cu:25-59):
+ *   LAYER_FIRST  base + layer * layout_dim + index * item_bytes        (layout_dim = bytes of one layer; a per-layer
+ *                                                                       call passes the layer's own base, layer 0)
+ *   PAGE_FIRST   base + index * layout_dim + layer * item_bytes        (layout_dim = bytes of one index across layers)
+ *   LAYER_TABLE  ((uint8_t*)table[layer]) + index * item_bytes         (`base` is a DEVICE array of uint64 pointers)
+ * src_indices / dst_indices: device int64 [n_items].  item_bytes must be a multiple of 8 (transfer.cu:142).
+ * block_quota > 0 caps the grid at that many CTAs (the reference's knob to leave SMs to a concurrent forward);
+ * 0 sizes the grid to the device. */
+#define B200ATTN_LAYOUT_LAYER_FIRST 0
+#define B200ATTN_LAYOUT_PAGE_FIRST 1
+#define B200ATTN_LAYOUT_LAYER_TABLE 2
+int b200attn_transfer_kv(const void* src_k, void* dst_k, const void* src_v, void* dst_v, int src_layout,
+                         int dst_layout, int64_t src_layout_dim, int64_t dst_layout_dim,
+                         const int64_t* src_indices, const int64_t* dst_indices, int64_t n_items,
+                         int64_t item_bytes, int start_layer, int num_layers, int block_quota,
+                         b200attn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -251,3 +251,23 @@ void orc_merge_state(const void* a, const float* lse_a, const void* b, const flo
     if (out_lse) out_lse[r] = s > 0 ? (float)(log(s) + m) : -INFINITY;
   }
 }
+
+/* ---------------------------------------------------------------- HiCache KV transfer
+ * Restates sgl-kernel/csrc/kvcacheio/transfer.cu:9-110: for every item and layer, copy item_bytes bytes from
+ * src(layer, src_idx[i]) to dst(layer, dst_idx[i]); layouts 0 = layer first (:25-35), 1 = page first (:37-47),
+ * 2 = per-layer pointer table (:49-59).  One buffer per call (K, V or the single MLA buffer). */
+static const uint8_t* orc_item_addr(const uint8_t* base, int layout, int64_t dim, int64_t layer, int64_t index,
+                                    int64_t item_bytes) {
+  if (layout == 0) return base + layer * dim + index * item_bytes;
+  if (layout == 1) return base + index * dim + layer * item_bytes;
+  return (const uint8_t*)(uintptr_t)(((const uint64_t*)base)[layer]) + index * item_bytes;
+}
+
+void orc_transfer_kv(const uint8_t* src, uint8_t* dst, int src_layout, int dst_layout, int64_t src_dim, int64_t dst_dim,
+                     const int64_t* src_idx, const int64_t* dst_idx, int64_t n_items, int64_t item_bytes,
+                     int64_t start_layer, int64_t num_layers) {
+  for (int64_t i = 0; i < n_items; ++i)
+    for (int64_t l = start_layer; l < start_layer + num_layers; ++l)
+      memcpy((uint8_t*)orc_item_addr(dst, dst_layout, dst_dim, l, dst_idx[i], item_bytes),
+             orc_item_addr(src, src_layout, src_dim, l, src_idx[i], item_bytes), (size_t)item_bytes);
+}

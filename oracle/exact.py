@@ -144,3 +144,17 @@ def merge_state(a, lse_a, b, lse_b):
     lib().orc_merge_state(_p(a), _p(lse_a.float().contiguous()), _p(b), _p(lse_b.float().contiguous()),
                           C.c_int64(T * H), C.c_int(D), C.c_int(_DT[a.dtype]), _p(out), _p(lse))
     return out, lse
+
+
+def transfer_kv(src: torch.Tensor, dst: torch.Tensor, src_layout: int, dst_layout: int, src_dim: int, dst_dim: int,
+                src_idx: torch.Tensor, dst_idx: torch.Tensor, item_bytes: int, num_layers: int, start_layer: int = 0):
+    """Plain-C restatement of the reference's transfer kernel (transfer.cu:9-110) on CPU tensors; `src`/`dst` are the
+    base buffers (layouts 0/1) or int64 tensors of per-layer data_ptr()s (layout 2)."""
+    _cpu(src, dst, src_idx, dst_idx)
+    L = lib()
+    L.orc_transfer_kv.restype = None
+    L.orc_transfer_kv.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                  C.c_int64, C.c_int64, C.c_int64, C.c_int64]
+    si, di = src_idx.to(torch.int64).contiguous(), dst_idx.to(torch.int64).contiguous()
+    L.orc_transfer_kv(src.data_ptr(), dst.data_ptr(), src_layout, dst_layout, src_dim, dst_dim, si.data_ptr(), di.data_ptr(),
+                      si.numel(), item_bytes, start_layer, num_layers)

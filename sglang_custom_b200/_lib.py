@@ -15,6 +15,7 @@ BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
 SCALE_DIV, SCALE_RCP = 0, 1
 EXTEND_AUTO, EXTEND_TCGEN05, EXTEND_MMA = 0, 1, 2
 ROPE_FP32, ROPE_NATIVE = 0, 1
+LAYOUT_LAYER_FIRST, LAYOUT_PAGE_FIRST, LAYOUT_LAYER_TABLE = 0, 1, 2
 
 ERR_NAMES = {0: "OK", -1: "INVALID", -2: "UNSUPPORTED", -3: "CUDA", -4: "WORKSPACE"}
 
@@ -42,6 +43,7 @@ SIGNATURES = {
                              _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
+    "b200attn_transfer_kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),
 }
 
 _lib = None
