@@ -9,7 +9,7 @@
 // the whole job is flattened into 16-byte chunks -- chunk g belongs to unit g / chunks_per_item, a unit being one
 // (item, layer, K|V) triple -- so consecutive threads always touch consecutive addresses whatever the item size
 // (the reference gives one warp a whole item with 8-byte accesses, which leaves lanes idle for items < 256 B and
-// keeps 256 B in flight per warp).  Every thread keeps four independent chunks in flight (all loads, then all
+// keeps 256 B in flight per warp).  Every thread keeps eight independent chunks in flight (all loads, then all
 // stores); the grid is capped at `block_quota` CTAs when the caller wants to leave SMs to a concurrent forward
 // (the reference's parameter of the same name), else sized to the device.
 #include "common.cuh"
@@ -53,9 +53,14 @@ __device__ __forceinline__ void st_stream(uint2* p, uint2 v) {
   asm volatile("st.global.cg.v2.u32 [%0], {%1, %2};\n" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
+// 1024 threads x 8 chunks x 16 B = 128 KiB in flight per CTA: the reference's default quota of two CTAs is then enough
+// to fill a PCIe 5 x16 link (measured: 2 CTAs of 256 threads x 4 chunks reach 4.6 GB/s host -> device, the link does 51)
+constexpr int kTransferThreads = 1024;
+constexpr int kTransferInFlight = 8;
+
 template <typename V>
-__global__ void __launch_bounds__(256) transfer_kernel(const TransferParams p) {
-  constexpr int kInFlight = 4;
+__global__ void __launch_bounds__(kTransferThreads) transfer_kernel(const TransferParams p) {
+  constexpr int kInFlight = kTransferInFlight;
   const int64_t cpi = p.item_bytes / static_cast<int64_t>(sizeof(V));  // chunks per item
   const int64_t units_per_item = static_cast<int64_t>(p.num_layers) * p.n_bufs;
   const int64_t total = p.n_items * units_per_item * cpi;
@@ -72,8 +77,9 @@ __global__ void __launch_bounds__(256) transfer_kernel(const TransferParams p) {
         const int64_t item = unit / units_per_item;
         const int r = static_cast<int>(unit % units_per_item);
         const int layer = p.start_layer + r / p.n_bufs, b = r % p.n_bufs;
-        const uint8_t* s = item_addr(p.src[b], p.src_layout, p.src_dim, layer, p.src_idx[item], p.item_bytes);
-        const uint8_t* d = item_addr(p.dst[b], p.dst_layout, p.dst_dim, layer, p.dst_idx[item], p.item_bytes);
+        // (ternaries, not p.src[b]: a runtime index into a kernel-parameter array forces a local-memory copy of it)
+        const uint8_t* s = item_addr(b ? p.src[1] : p.src[0], p.src_layout, p.src_dim, layer, p.src_idx[item], p.item_bytes);
+        const uint8_t* d = item_addr(b ? p.dst[1] : p.dst[0], p.dst_layout, p.dst_dim, layer, p.dst_idx[item], p.item_bytes);
         val[u] = ld_stream<V>(reinterpret_cast<const V*>(s) + c);
         out[u] = const_cast<V*>(reinterpret_cast<const V*>(d)) + c;
       }
@@ -126,12 +132,13 @@ extern "C" B2_EXPORT int b200attn_transfer_kv(const void* src_k, void* dst_k, co
                    (!src_v || (ok16(src_v, src_layout, src_layout_dim) && ok16(dst_v, dst_layout, dst_layout_dim)));
   const int64_t chunk = v16 ? 16 : 8;
   const int64_t total = n_items * num_layers * p.n_bufs * (item_bytes / chunk);
-  int64_t blocks = (total + 256 * 4 - 1) / (256 * 4);
-  const int64_t cap = block_quota > 0 ? block_quota : static_cast<int64_t>(sm_count()) * 4;
+  const int64_t per_cta = static_cast<int64_t>(kTransferThreads) * kTransferInFlight;
+  int64_t blocks = (total + per_cta - 1) / per_cta;
+  const int64_t cap = block_quota > 0 ? block_quota : static_cast<int64_t>(sm_count()) * 2;
   if (blocks > cap) blocks = cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (v16) transfer_kernel<uint4><<<static_cast<unsigned>(blocks), 256, 0, st>>>(p);
-  else transfer_kernel<uint2><<<static_cast<unsigned>(blocks), 256, 0, st>>>(p);
+  if (v16) transfer_kernel<uint4><<<static_cast<unsigned>(blocks), kTransferThreads, 0, st>>>(p);
+  else transfer_kernel<uint2><<<static_cast<unsigned>(blocks), kTransferThreads, 0, st>>>(p);
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
 }

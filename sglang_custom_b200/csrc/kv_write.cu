@@ -27,10 +27,16 @@ struct KvWriteParams {
 // kMode 0: same-dtype bit copy. kMode 1: 16-bit float -> e4m3 with optional scale.
 template <bool kBf16, int kMode>
 __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
-  const int which = blockIdx.y;
+  // (ternaries, not p.src[blockIdx.y]: a runtime index into a kernel-parameter array forces a local-memory copy)
+  const bool is_v = blockIdx.y != 0;
   const int chunks_per_row = p.D >> 3;
   const int64_t total = static_cast<int64_t>(p.T) * p.Hkv * chunks_per_row;
-  const uint16_t* __restrict__ src = reinterpret_cast<const uint16_t*>(p.src[which]);
+  const uint16_t* __restrict__ src = reinterpret_cast<const uint16_t*>(is_v ? p.src[1] : p.src[0]);
+  void* const pool = is_v ? p.pool[1] : p.pool[0];
+  const int64_t tok_stride = is_v ? p.tok_stride[1] : p.tok_stride[0];
+  const int64_t head_stride = is_v ? p.head_stride[1] : p.head_stride[0];
+  const float* const scale_dev = is_v ? p.scale_dev[1] : p.scale_dev[0];
+  const float scale_host = is_v ? p.scale_host[1] : p.scale_host[0];
   for (int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; c < total;
        c += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int ch = static_cast<int>(c % chunks_per_row);
@@ -38,17 +44,17 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
     const int h = static_cast<int>(th % p.Hkv);
     const int64_t t = th / p.Hkv;
     const int64_t slot = p.loc[t];
-    const uint16_t* s = src + t * p.tok_stride[which] + h * p.head_stride[which] + ch * 8;
+    const uint16_t* s = src + t * tok_stride + h * head_stride + ch * 8;
     const uint4 in = *reinterpret_cast<const uint4*>(s);
     const int64_t dst_elem = slot * p.pool_tok_stride + static_cast<int64_t>(h) * p.D + ch * 8;
     if constexpr (kMode == 0) {
-      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.pool[which]) + dst_elem) = in;
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(pool) + dst_elem) = in;
     } else {
-      float scale = p.scale_host[which];
-      if (p.scale_dev[which] != nullptr) scale = p.scale_dev[which][p.n_scales > 1 ? h : 0];
+      float scale = scale_host;
+      if (scale_dev != nullptr) scale = scale_dev[p.n_scales > 1 ? h : 0];
       uint4 back;
       const uint2 q8 = quantize_chunk_e4m3<kBf16>(in, scale, p.scale_mode, back);
-      *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.pool[which]) + dst_elem) = q8;
+      *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(pool) + dst_elem) = q8;
       if (p.writeback && scale != 0.0f) *reinterpret_cast<uint4*>(const_cast<uint16_t*>(s)) = back;
     }
   }

@@ -150,6 +150,27 @@ def test_mixed_batch_prefill_rows_plus_decode_tail(kw, device):
     H.assert_close(got3, H.oracle_extend(case1, kp, vp), what="all-tail extend")
 
 
+def test_c5_shaped_mixed_forward_scaled_down(device):
+    """BASELINE config 5 at 1/8 scale, per-rank TP 8 shape (8 Q / 1 KV head, FP8 KV, page_size 16): one MIXED
+    forward of chunked-prefill rows (prefix a multiple of the page size, 128-token chunk) followed by running decode
+    rows with ragged lengths; the generator is the one scripts/time_mixed.py runs at full size."""
+    g = torch.Generator().manual_seed(5)
+    n_dec, n_ext = 31, 2
+    ext_prefix = (16 * torch.randint(0, 1536 // 8, (n_ext,), generator=g)).tolist()
+    dec_lens = torch.randint(1024 // 8, 32768 // 8 + 1, (n_dec,), generator=g).tolist()
+    E = 128
+    lens = [p + E for p in ext_prefix] + dec_lens
+    ext = [E] * n_ext + [1] * n_dec
+    case = synth.make_case(len(lens), 8, 1, 128, lens, extend_lens=ext, fp8=True, kv_scale=0.1135, page_size=16, seed=1239)
+    kp, vp = H.pool_after_write(case)
+    r = H.Runner(case, device)
+    got = r.forward(r.itf.ForwardMode.MIXED)
+    dk, dv = r.pools()
+    assert H.pools_equal(dk, kp) and H.pools_equal(dv, vp), "FP8 KV write of the mixed forward"
+    assert r.backend.forward_metadata.n_decode_tail == n_dec
+    H.assert_close(got, H.oracle_extend(case, kp, vp), what="C5-shaped mixed forward")
+
+
 def test_extend_chunked_prefill_equals_one_shot(device):
     """Chunked prefill (scheduler.py:452-457): chunk 2 sees chunk 1 as cached prefix; same result as one extend."""
     L = 700
