@@ -20,6 +20,8 @@
  *                                sgl-kernel/csrc/attention/merge_attn_states.cu:32-106
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
  *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
+ *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
+ *   b200attn_extend_masked       triton_ops/extend_attention.py:158-175,236-247 (sliding window, custom mask)
  *   b200attn_flatten_kv_indices  layers/attention/utils.py:5-41 (create_flashinfer_kv_indices_triton)
  *   b200attn_gather_kv           torch_native_backend.py:92-94,155-157 (k_cache[per_req_tokens] page gather)
  *
@@ -131,13 +133,22 @@ int b200attn_rope_kv_write(void* q, int64_t q_tok_stride, void* k, int64_t k_tok
  * that falls entirely inside one share is finished by that CTA; a request cut
  * across shares produces one fp32 partial per share, combined by the LSE merge.
  *
- * plan layout (int32): [0] total_units [1] W [2] bs [3] n_ctas [4..7] reserved,
+ * plan layout (int32): [0] total_units [1] W [2] bs [3] n_ctas [4] sliding_window_size (-1: none) [5..7] reserved,
  *   then cum[bs+1] (exclusive prefix sum of units), then first_req[n_ctas].
  */
 size_t b200attn_decode_plan_bytes(int max_bs, int n_ctas);
 int b200attn_decode_plan(const void* seq_lens, int idx_is_i64, int bs, int n_ctas,
                          int min_units_per_cta, int32_t* plan, size_t plan_bytes,
                          b200attn_stream_t stream);
+
+/* Plan for sliding-window layers (layer.sliding_window_size > -1): request i contributes only its last
+ * min(seq_lens[i], sliding_window_size + 1) tokens, i.e. what update_sliding_window_buffer
+ * (triton_backend.py:927-955) flattens into window_kv_indices for TritonAttnBackend.forward_decode
+ * (triton_backend.py:711-716).  The window is stored in plan[4]; b200attn_decode / _partial read it from the
+ * plan, so a model that mixes local and global layers keeps two plan buffers and nothing else changes. */
+int b200attn_decode_plan_window(const void* seq_lens, int idx_is_i64, int bs, int n_ctas,
+                                int min_units_per_cta, int sliding_window_size, int32_t* plan,
+                                size_t plan_bytes, b200attn_stream_t stream);
 
 /* fp32 workspace for split partials: 2 * n_ctas * Hq * (Dv + 1) floats */
 size_t b200attn_decode_workspace_bytes(int n_ctas, int Hq, int Dv);
@@ -204,6 +215,32 @@ int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_
                     int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
                     float logit_cap, float k_scale, float v_scale, int causal, int impl, float* lse_out,
                     b200attn_stream_t stream);
+
+/* Extend with the two extra predicates of TritonAttnBackend.forward_extend (triton_backend.py:658-684 ->
+ * triton_ops/extend_attention.py:42-303): a sliding window and a speculative-decoding custom mask
+ * (TARGET_VERIFY batches, triton_backend.py:227-264).  All other arguments as b200attn_extend.
+ *   sliding_window_size  -1: none.  W >= 0: of the P_i cached-prefix keys only the last Wp = min(P_i, W + 1) are read
+ *                        (window_kv_indices, triton_backend.py:299-309,927-955) and, for W > 0, the key at offset jw
+ *                        in [0, Wp) of that range is visible to query t (0-based inside the request's new tokens)
+ *                        iff t <= jw + W (extend_attention.py:168-174).  New-token keys keep the plain causal rule:
+ *                        the reference applies no window there, and neither does this kernel.
+ *   custom_mask          NULL: none.  uint8/bool, request i's block starts at mask_indptr[i] (int64 [bs+1], bytes)
+ *                        and is [E_i, L_i] row-major with L_i = P_i + E_i.  A new-token key j >= P_i is visible to
+ *                        query t iff mask[t, j] != 0 and (causal == 0 or j <= P_i + t); cached-prefix keys consult
+ *                        the mask only when skip_prefix_custom_mask == 0 (the reference backend always passes the
+ *                        default skip = True, extend_attention.py:322).  EAGLE tree masks are subsets of the causal
+ *                        mask, for which this is exactly the reference's predicate.
+ *   A query whose keys are all masked produces 0 (the reference's online softmax produces NaN there).
+ * Served by the register-MMA kernel (verify batches are num_draft_tokens rows per request). */
+int b200attn_extend_masked(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                           const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                           const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                           const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
+                           const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
+                           int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                           float logit_cap, float k_scale, float v_scale, int causal, int sliding_window_size,
+                           const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask,
+                           float* lse_out, b200attn_stream_t stream);
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */
 #define B200ATTN_EXTEND_MMA 2     /* register-MMA kernel (short / ragged rows, FP8 KV, D == 64) */

@@ -32,6 +32,7 @@ SIGNATURES = {
                                     _vp, _vp, _i64, _i, _f, _f, _vp, _vp, _i, _i, _i, _vp]),
     "b200attn_decode_plan_bytes": (_sz, [_i, _i]),
     "b200attn_decode_plan": (_i, [_vp, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "b200attn_decode_plan_window": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "b200attn_decode_workspace_bytes": (_sz, [_i, _i, _i]),
     "b200attn_decode": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i,
                              _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _vp]),
@@ -41,6 +42,8 @@ SIGNATURES = {
     "b200attn_merge_state": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b200attn_extend": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
                              _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _vp, _vp]),
+    "b200attn_extend_masked": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
+                                    _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _vp, _vp, _i, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200attn_transfer_kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),

@@ -70,6 +70,13 @@ class ForwardMetadata:
     # MIXED batches: the running (decode) requests are appended after the prefill requests with
     # extend_len = 1 (schedule_batch.py:1310-1338); that tail is served by the decode kernel
     n_decode_tail: int = 0
+    # TARGET_VERIFY (speculative decoding): every request contributes num_draft_tokens query rows over its
+    # seq_lens cached tokens; built on the device, no host sync (triton_backend.py:227-264)
+    extend_seq_lens: Optional[torch.Tensor] = None
+    extend_prefix_lens: Optional[torch.Tensor] = None
+    total_lens: Optional[torch.Tensor] = None
+    custom_mask: Optional[torch.Tensor] = None
+    mask_indptr: Optional[torch.Tensor] = None
 
 
 class B200AttnBackend(AttentionBackend):
@@ -84,9 +91,11 @@ class B200AttnBackend(AttentionBackend):
             raise B200AttnError(f"libb200attn.so is built for sm_100a only, found compute capability "
                                 f"{info['cc_major']}.{info['cc_minor']}")
         self.skip_prefill = skip_prefill
+        # sliding-window models (triton_backend.py:124): window layers read the last min(L, W + 1) tokens
         sw = getattr(model_runner, "sliding_window_size", None)
-        if sw is not None and sw > 0:
-            raise NotImplementedError("b200 attention backend: sliding-window attention is not built")
+        self.sliding_window_size = int(sw) if sw is not None and sw > 0 else None
+        sargs = getattr(model_runner, "server_args", None)
+        self.num_draft_tokens = getattr(sargs, "speculative_num_draft_tokens", None)
         if getattr(model_runner.model_config, "is_encoder_decoder", False):
             raise NotImplementedError("b200 attention backend: encoder-decoder (cross attention) is not built")
 
@@ -116,25 +125,34 @@ class B200AttnBackend(AttentionBackend):
         self.plan = torch.zeros(ops.decode_plan_bytes(max_bs, self.n_ctas) // 4, dtype=torch.int32, device=self.device)
         ws = ops.decode_workspace_bytes(self.n_ctas, self.num_head, self.v_head_dim)
         self.workspace = torch.empty(ws // 4, dtype=torch.float32, device=self.device)
+        # second plan for sliding-window layers (the reference keeps window_kv_indptr / window_kv_indices beside
+        # kv_indptr / kv_indices, triton_backend.py:124-135)
+        self.window_plan = torch.zeros_like(self.plan) if self.sliding_window_size is not None else None
 
     # ------------------------------------------------------------------ metadata
     def init_forward_metadata(self, forward_batch):
         """One tiny device-side kernel (decode) or nothing at all (extend): no flattened kv_indices
         copy, no host sync (the reference syncs on max_extend_len, triton_backend.py:320)."""
-        if getattr(forward_batch, "spec_info", None) is not None:
-            raise NotImplementedError("b200 attention backend: speculative decoding (spec_info) is not built")
         bs = forward_batch.batch_size
         mode = forward_batch.forward_mode
+        spec_info = getattr(forward_batch, "spec_info", None)
+        if spec_info is not None:
+            if not (hasattr(mode, "is_target_verify") and mode.is_target_verify()):
+                raise NotImplementedError("b200 attention backend: of the speculative-decoding modes only "
+                                          "TARGET_VERIFY is built (no DRAFT_EXTEND / multi-step draft decode)")
+            self.forward_metadata = self._verify_metadata(len(forward_batch.req_pool_indices), forward_batch.seq_lens,
+                                                          spec_info, None)
+            return
         if mode.is_decode_or_idle():
             if bs > 0:
-                ops.decode_plan(forward_batch.seq_lens, self.n_ctas, self.plan, self.min_units_per_cta)
+                self._plan_decode(forward_batch.seq_lens)
             self.forward_metadata = ForwardMetadata(True, bs)
             return
         ext_cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
         n_tail = 0
         if ext_cpu is not None:
             ext_cpu = list(ext_cpu)
-            if self.route_decode_tail:
+            if self.route_decode_tail and self.sliding_window_size is None:
                 while n_tail < len(ext_cpu) and ext_cpu[len(ext_cpu) - 1 - n_tail] == 1:
                     n_tail += 1
             head = ext_cpu[:len(ext_cpu) - n_tail]
@@ -147,9 +165,47 @@ class B200AttnBackend(AttentionBackend):
             start = (torch.cumsum(ext, 0) - ext).to(torch.int32)
         if n_tail:
             # a query with extend_len 1 at position L-1 sees all L keys: exactly a decode row
-            ops.decode_plan(forward_batch.seq_lens[bs - n_tail:], self.n_ctas, self.plan, self.min_units_per_cta)
+            self._plan_decode(forward_batch.seq_lens[bs - n_tail:])
         self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend,
                                                 n_decode_tail=n_tail)
+
+    def _plan_decode(self, seq_lens) -> None:
+        ops.decode_plan(seq_lens, self.n_ctas, self.plan, self.min_units_per_cta)
+        if self.window_plan is not None:
+            ops.decode_plan(seq_lens, self.n_ctas, self.window_plan, self.min_units_per_cta,
+                            sliding_window_size=self.sliding_window_size)
+
+    def _verify_metadata(self, bs: int, seq_lens, spec_info, bufs) -> ForwardMetadata:
+        """TARGET_VERIFY (triton_backend.py:227-264): qo_indptr = arange * num_draft_tokens, the prefix is seq_lens
+        (the draft tokens' slots sit behind it in req_to_token: eagle_utils.py:268-276), mask block i is
+        [num_draft_tokens, seq_lens[i] + num_draft_tokens].  `bufs` = fixed CUDA-graph buffers to fill in place."""
+        nd = self.num_draft_tokens or getattr(spec_info, "draft_token_num", None)
+        if not nd:
+            raise B200AttnError("TARGET_VERIFY needs server_args.speculative_num_draft_tokens")
+        nd = int(nd)
+        sl = seq_lens[:bs]
+        prefix = sl.to(torch.int32)
+        if bufs is None:
+            ext = torch.full((bs,), nd, dtype=torch.int32, device=self.device)
+            start = torch.arange(0, bs * nd, nd, dtype=torch.int32, device=self.device)
+            total = sl + nd
+            mask_indptr = torch.zeros(bs + 1, dtype=torch.int64, device=self.device)
+            mask_indptr[1:] = torch.cumsum(nd * (sl.to(torch.int64) + nd), 0)
+            mask = spec_info.custom_mask
+        else:
+            ext, pre, start, total, mask_indptr, mask = (b[:n] for b, n in zip(
+                bufs, (bs, bs, bs, bs, bs + 1, bufs[5].numel())))
+            ext.fill_(nd)
+            pre.copy_(prefix)
+            prefix = pre
+            start.copy_(torch.arange(0, bs * nd, nd, dtype=torch.int32, device=self.device))
+            total.copy_(sl + nd)
+            mask_indptr[1:] = torch.cumsum(nd * (sl.to(torch.int64) + nd), 0)
+            n = spec_info.custom_mask.numel()
+            mask[:n] = spec_info.custom_mask.view(torch.uint8) if spec_info.custom_mask.dtype == torch.bool \
+                else spec_info.custom_mask
+        return ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=nd, extend_seq_lens=ext,
+                               extend_prefix_lens=prefix, total_lens=total, custom_mask=mask, mask_indptr=mask_indptr)
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -157,23 +213,42 @@ class B200AttnBackend(AttentionBackend):
         if max_bs > self.max_bs:
             self.max_bs = max_bs
             self._alloc_decode_buffers(max_bs)
+        if self.num_draft_tokens and not self.skip_prefill:
+            # TARGET_VERIFY graphs: fixed-address lens / mask buffers (triton_backend.py:366-371)
+            i32 = dict(dtype=torch.int32, device=self.device)
+            self.cg_verify = (torch.zeros(max_bs, **i32), torch.zeros(max_bs, **i32), torch.zeros(max_bs, **i32),
+                              torch.zeros(max_bs, **i32), torch.zeros(max_bs + 1, dtype=torch.int64, device=self.device),
+                              torch.zeros(max_num_tokens * self.max_context_len, dtype=torch.uint8, device=self.device))
 
     def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens, encoder_lens,
                                                  forward_mode, spec_info):
         if encoder_lens is not None:
             raise NotImplementedError("b200 attention backend: encoder_lens is not supported")
-        if spec_info is not None or not forward_mode.is_decode_or_idle():
-            raise NotImplementedError("b200 attention backend: only DECODE batches run under CUDA graphs")
-        ops.decode_plan(seq_lens[:bs], self.n_ctas, self.plan, self.min_units_per_cta)
-        self.forward_metadata = ForwardMetadata(True, bs, req_pool_indices=req_pool_indices[:bs], seq_lens=seq_lens[:bs])
+        if forward_mode.is_decode_or_idle() and spec_info is None:
+            self._plan_decode(seq_lens[:bs])
+            self.forward_metadata = ForwardMetadata(True, bs, req_pool_indices=req_pool_indices[:bs],
+                                                    seq_lens=seq_lens[:bs])
+            return
+        if hasattr(forward_mode, "is_target_verify") and forward_mode.is_target_verify() and spec_info is not None:
+            if getattr(self, "cg_verify", None) is None:
+                raise B200AttnError("TARGET_VERIFY capture before init_cuda_graph_state / without num_draft_tokens")
+            md = self._verify_metadata(bs, seq_lens, spec_info, self.cg_verify)
+            md.req_pool_indices = req_pool_indices[:bs]
+            self.forward_metadata = md
+            return
+        raise NotImplementedError("b200 attention backend: only DECODE and TARGET_VERIFY batches run under CUDA graphs")
 
     def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens,
                                                 forward_mode, spec_info, seq_lens_cpu):
         """Runs right before graph.replay(): refresh the plan in place from the (device) seq_lens.
         Padded rows arrive as seq_len = 1 / req_pool_idx = 0 (cuda_graph_runner.py:686-695)."""
-        if spec_info is not None or not forward_mode.is_decode_or_idle():
-            raise NotImplementedError("b200 attention backend: only DECODE batches run under CUDA graphs")
-        ops.decode_plan(seq_lens[:bs], self.n_ctas, self.plan, self.min_units_per_cta)
+        if forward_mode.is_decode_or_idle() and spec_info is None:
+            self._plan_decode(seq_lens[:bs])
+            return
+        if hasattr(forward_mode, "is_target_verify") and forward_mode.is_target_verify() and spec_info is not None:
+            self._verify_metadata(bs, seq_lens, spec_info, self.cg_verify)  # refills the captured buffers in place
+            return
+        raise NotImplementedError("b200 attention backend: only DECODE and TARGET_VERIFY batches run under CUDA graphs")
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
@@ -184,9 +259,18 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("b200 attention backend: cross attention is not built")
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("b200 attention backend: qk_head_dim != v_head_dim (MLA) is not built")
+
+    def _layer_window(self, layer) -> int:
+        """-1 for a global layer, else the layer's window -- which must be the one the window plan was built for
+        (the reference builds window_kv_indices from the backend's size and masks with the layer's,
+        triton_backend.py:187-201,658-665; a model has one window size)."""
         sw = getattr(layer, "sliding_window_size", None)
-        if sw is not None and sw > -1:
-            raise NotImplementedError("b200 attention backend: sliding-window layers are not built")
+        if sw is None or sw <= -1:
+            return -1
+        if self.sliding_window_size is None or int(sw) != self.sliding_window_size:
+            raise B200AttnError(f"layer.sliding_window_size={sw} but the backend was built for "
+                                f"model_runner.sliding_window_size={self.sliding_window_size}")
+        return int(sw)
 
     @staticmethod
     def _kv_scales(layer):
@@ -225,9 +309,11 @@ class B200AttnBackend(AttentionBackend):
         # the layer_transfer_counter wait (HiCache) lives in get_key_buffer (memory_pool.py:401-402)
         pool.get_key_buffer(layer.layer_id)
         k_scale, v_scale = self._kv_scales(layer)
+        # sliding-window layers: same kernel, the plan that covers the last min(L, W + 1) tokens
+        plan = self.window_plan if self._layer_window(layer) > -1 else self.plan
         ops.decode(q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
                    o.view(-1, layer.tp_q_head_num, layer.v_head_dim), pool.k_buffer[lid], pool.v_buffer[lid],
-                   forward_batch.req_to_token_pool.req_to_token, rpi, sl, self.plan, self.n_ctas, self.workspace,
+                   forward_batch.req_to_token_pool.req_to_token, rpi, sl, plan, self.n_ctas, self.workspace,
                    layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0, k_scale, v_scale, kv_dtype=pool.dtype)
         return o
 
@@ -250,6 +336,16 @@ class B200AttnBackend(AttentionBackend):
         o3 = o.view(-1, layer.tp_q_head_num, layer.v_head_dim)
         table = forward_batch.req_to_token_pool.req_to_token
         cap = getattr(layer, "logit_cap", 0.0) or 0.0
+        window = self._layer_window(layer)
+        if md.custom_mask is not None:  # TARGET_VERIFY
+            if window > -1:  # the reference has no window in spec inference either (triton_backend.py:228)
+                raise NotImplementedError("b200 attention backend: sliding window with speculative decoding")
+            rpi = md.req_pool_indices if md.req_pool_indices is not None else forward_batch.req_pool_indices
+            ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi[:md.bs], md.total_lens,
+                       md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, md.max_extend_len,
+                       layer.scaling, cap, k_scale, v_scale, causal=causal, kv_dtype=pool.dtype,
+                       custom_mask=md.custom_mask, mask_indptr=md.mask_indptr)
+            return o
         n_tail = md.n_decode_tail  # a 1-token row sees all L keys with or without the causal mask
         n_ext = md.bs - n_tail
         t_ext = q3.shape[0] - n_tail
@@ -258,8 +354,11 @@ class B200AttnBackend(AttentionBackend):
                        forward_batch.req_pool_indices[:n_ext], forward_batch.seq_lens[:n_ext],
                        forward_batch.extend_seq_lens[:n_ext], forward_batch.extend_prefix_lens[:n_ext],
                        md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling, cap, k_scale, v_scale,
-                       causal=causal, kv_dtype=pool.dtype)
+                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window)
         if n_tail > 0:
+            # (window layers: a 1-token row's prefix range is its last min(L - 1, W + 1) cached tokens plus itself --
+            #  the decode window plan keeps min(L, W + 1); the two differ by one key, so window layers keep the tail
+            #  on the extend kernel: route_decode_tail is ignored for them in init_forward_metadata)
             ops.decode(q3[t_ext:], o3[t_ext:], pool.k_buffer[lid], pool.v_buffer[lid], table,
                        forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan, self.n_ctas,
                        self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)

@@ -230,14 +230,16 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
           while (cum[i + 1] <= u) ++i;
           const int c0 = cum[i], c1 = cum[i + 1];
           const int seg_end = min(c1, u_end);
-          const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
+          const int Lfull = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, i));
+          const int win = p.plan[kPlanWindow];  // sliding-window plan: only the last min(L, win + 1) tokens
+          const int L = (win >= 0 && Lfull > win + 1) ? win + 1 : Lfull;
           Segment s;
           s.batch = i;
           s.tok_begin = (u - c0) * kUnit;
           s.tok_end = min((seg_end - c0) * kUnit, L);
           const bool is_first = (u == c0), is_last = (seg_end == c1);
           s.slot = (is_first && is_last) ? -1 : (is_first ? 2 * cta + 1 : 2 * cta);
-          s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride;
+          s.table_off = load_index(p.req_pool_indices, p.idx_is_i64, i) * p.table_stride + (Lfull - L);
           segs[n++] = s;
           u = seg_end;
         }

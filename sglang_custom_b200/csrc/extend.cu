@@ -8,15 +8,14 @@
 
 using namespace b200attn;
 
-extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
-                                         const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
-                                         const int32_t* req_to_token, int64_t table_stride,
-                                         const void* req_pool_indices, const void* seq_lens, int idx_is_i64,
-                                         const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
-                                         const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq,
-                                         int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale, float logit_cap,
-                                         float k_scale, float v_scale, int causal, int impl, float* lse_out,
-                                         b200attn_stream_t stream) {
+static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool,
+                       const void* v_pool, int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride,
+                       const void* req_pool_indices, const void* seq_lens, int idx_is_i64,
+                       const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+                       const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D,
+                       int q_dtype, int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
+                       int causal, int impl, float* lse_out, int window, const uint8_t* custom_mask,
+                       const int64_t* mask_indptr, int skip_prefix_mask, b200attn_stream_t stream) {
   B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0 && max_extend_len >= 0, B200ATTN_ERR_INVALID,
              "extend: bad sizes bs=%d Hq=%d Hkv=%d max_extend_len=%d", bs, Hq, Hkv, max_extend_len);
   if (bs == 0 || max_extend_len == 0) return B200ATTN_OK;
@@ -52,6 +51,7 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   p.scale_log2 = sm_scale * k_scale * kLog2e;
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
+  p.window = window; p.custom_mask = custom_mask; p.mask_indptr = mask_indptr; p.skip_prefix_mask = skip_prefix_mask;
   {
     // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
     static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 0; }();
@@ -64,6 +64,14 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool q_bf16 = q_dtype == B200ATTN_BF16;
+  if (window >= 0 || custom_mask != nullptr) {
+    // the predicate lives in the register-MMA kernel only (verify batches are a few rows per request)
+    B2_REQUIRE(impl != B200ATTN_EXTEND_TCGEN05, B200ATTN_ERR_UNSUPPORTED,
+               "extend: the tcgen05 kernel has no sliding-window / custom-mask predicate");
+    B2_REQUIRE(custom_mask == nullptr || mask_indptr != nullptr, B200ATTN_ERR_INVALID,
+               "extend: custom_mask without mask_indptr");
+    return extend_mma_masked_launch(p, D, kvb, q_bf16, st);
+  }
   const bool tc_ok = extend_tc_supported(p, D, kvb);
   if (impl == B200ATTN_EXTEND_TCGEN05) {
     B2_REQUIRE(tc_ok, B200ATTN_ERR_UNSUPPORTED,
@@ -75,4 +83,38 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   // batch, tiny chunks) are not worth a 128-row tile.
   if (impl == B200ATTN_EXTEND_AUTO && tc_ok && max_extend_len >= 128) return extend_tc_launch(p, q_bf16, kvb, st);
   return extend_mma_launch(p, D, kvb, q_bf16, st);
+}
+
+extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                                         const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                                         const int32_t* req_to_token, int64_t table_stride,
+                                         const void* req_pool_indices, const void* seq_lens, int idx_is_i64,
+                                         const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+                                         const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq,
+                                         int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale, float logit_cap,
+                                         float k_scale, float v_scale, int causal, int impl, float* lse_out,
+                                         b200attn_stream_t stream) {
+  return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
+                     table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
+                     extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
+                     k_scale, v_scale, causal, impl, lse_out, -1, nullptr, nullptr, 1, stream);
+}
+
+// Sliding-window layers and speculative-decoding verify batches: TritonAttnBackend.forward_extend with
+// window_kv_indices / custom_mask (triton_backend.py:227-264,299-309,658-684; kernel predicate
+// triton_ops/extend_attention.py:158-175,236-247).
+extern "C" B2_EXPORT int b200attn_extend_masked(
+    const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool, const void* v_pool,
+    int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+    const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+    const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,
+    float sm_scale, float logit_cap, float k_scale, float v_scale, int causal, int sliding_window_size,
+    const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask, float* lse_out,
+    b200attn_stream_t stream) {
+  B2_REQUIRE(sliding_window_size >= -1, B200ATTN_ERR_INVALID, "extend_masked: sliding_window_size=%d", sliding_window_size);
+  return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
+                     table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
+                     extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
+                     k_scale, v_scale, causal, B200ATTN_EXTEND_MMA, lse_out, sliding_window_size, custom_mask,
+                     mask_indptr, skip_prefix_custom_mask, stream);
 }

@@ -26,11 +26,24 @@ struct ExtendParams {
   float v_scale;
   unsigned long long* prof;  // B200ATTN_PROF_PTR: device buffer for clock64 phase timings of CTA (0,0,0) (dev only)
   int grid_order;  // tcgen05 kernel: 0 = (head pair, request, q tile), 1 = (head pair, q tile, request)  (B200ATTN_GRID_ORDER)
+  // ---- masked variant (extend_mma.cu, kMasked): sliding window and speculative-decoding custom mask
+  // window >= 0: only the last min(P, window+1) cached-prefix keys are read (update_sliding_window_buffer,
+  // triton_backend.py:927-955) and, for window > 0, a prefix key at offset jw inside that range is visible to
+  // query t iff t <= jw + window (extend_attention.py:168-174); new-token keys stay causal (no window mask there).
+  int window;
+  // custom_mask != NULL: uint8/bool, request i's block starts at mask_indptr[i] and is [E_i, L_i] row-major;
+  // new-token keys take mask (and causal), cached-prefix keys take it only when skip_prefix_mask == 0
+  // (extend_attention.py:158-167,236-247)
+  const uint8_t* custom_mask;
+  const int64_t* mask_indptr;
+  int skip_prefix_mask;
   int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 0: measured best at C3)
 };
 
 // register-MMA kernel (extend_mma.cu): any shape the library accepts
 int extend_mma_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaStream_t st);
+// same kernel compiled with the window / custom-mask predicate (p.window >= 0 or p.custom_mask != NULL)
+int extend_mma_masked_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaStream_t st);
 
 // tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit or FP8-E4M3 KV, logit_cap == 0
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb);

@@ -36,7 +36,7 @@ struct ExtCfg {
   static_assert(CHUNKS % kExtThreads == 0, "tile must divide over the CTA");
 };
 
-template <int D, int KVB, bool kQBf16>
+template <int D, int KVB, bool kQBf16, bool kMasked>
 __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendParams p) {
   using Cfg = ExtCfg<D, KVB>;
   constexpr bool kFp8 = (KVB == 1);
@@ -62,6 +62,12 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
   const int q_hi = min(q0 + kExtBM, E);                       // one past the last query of this tile
   const int kv_end = p.causal ? min(L, P + q_hi) : L;         // keys any row of the tile can see
   const int ntiles = (kv_end + BN - 1) / BN;
+  // masked variant: first prefix key inside the sliding window (0 without a window) and its tile
+  int kv_begin = 0;
+  if constexpr (kMasked) {
+    if (p.window >= 0) kv_begin = P - min(P, p.window + 1);
+  }
+  const int tile0 = kv_begin / BN;
 
   const uint8_t* kpool = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * Cfg::HEADB;
   const uint8_t* vpool = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * Cfg::HEADB;
@@ -70,7 +76,7 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
   auto stage_indices = [&](int t) {
     if (t < ntiles && tid < BN) {
       const int tok = t * BN + tid;
-      idx_ring[(t % 3) * BN + tid] = tok < kv_end ? __ldg(trow + tok) : -1;
+      idx_ring[(t % 3) * BN + tid] = (tok < kv_end && tok >= kv_begin) ? __ldg(trow + tok) : -1;
     }
   };
   auto issue_tile = [&](int t) {
@@ -92,10 +98,10 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
     cp_async_commit();
   };
 
-  stage_indices(0);
-  stage_indices(1);
+  stage_indices(tile0);
+  stage_indices(tile0 + 1);
   __syncthreads();
-  issue_tile(0);
+  issue_tile(tile0);
 
   // ---- Q fragments: rows = 16 queries of this warp (zero for rows past E)
   const int t0 = q0 + warp * 16 + row, t1 = t0 + 8;  // query index inside the request
@@ -142,7 +148,24 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
   for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
-  for (int t = 0; t < ntiles; ++t) {
+  // masked variant: per-row predicate pieces
+  //   prefix key j (kv_begin <= j < P) needs j >= lo (window rule t <= (j - kv_begin) + window)
+  int lo0 = kv_begin, lo1 = kv_begin;
+  const uint8_t* mrow0 = nullptr;
+  const uint8_t* mrow1 = nullptr;
+  if constexpr (kMasked) {
+    if (p.window > 0) {
+      lo0 = kv_begin + max(0, t0 - p.window);
+      lo1 = kv_begin + max(0, t1 - p.window);
+    }
+    if (p.custom_mask != nullptr) {
+      const uint8_t* mb = p.custom_mask + p.mask_indptr[req];
+      mrow0 = mb + static_cast<int64_t>(min(t0, E - 1)) * L;
+      mrow1 = mb + static_cast<int64_t>(min(t1, E - 1)) * L;
+    }
+  }
+
+  for (int t = tile0; t < ntiles; ++t) {
     issue_tile(t + 1);
     stage_indices(t + 2);
     cp_async_wait<1>();
@@ -194,7 +217,11 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
           if (p.logit_cap > 0.f) x = p.logit_cap * fast_tanh(s[nb][e] * p.scale_raw / p.logit_cap) * kLog2e;
           else x = s[nb][e] * p.scale_log2;
           const int j = kv0 + nb * 8 + 2 * qd + (e & 1);
-          const bool ok = j < ((e & 2) ? vis1 : vis0);
+          bool ok = j < ((e & 2) ? vis1 : vis0);
+          if constexpr (kMasked) {
+            if (j < P) ok = ok && j >= ((e & 2) ? lo1 : lo0);
+            if (mrow0 != nullptr && ok && (j >= P || !p.skip_prefix_mask)) ok = __ldg(((e & 2) ? mrow1 : mrow0) + j) != 0;
+          }
           x = ok ? x : -INFINITY;
           s[nb][e] = x;
           if (e & 2) mx1 = fmaxf(mx1, x); else mx0 = fmaxf(mx0, x);
@@ -295,10 +322,10 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
   }
 }
 
-template <int D, int KVB, bool kQBf16>
+template <int D, int KVB, bool kQBf16, bool kMasked = false>
 static int launch_mma(const ExtendParams& p, cudaStream_t st) {
   using Cfg = ExtCfg<D, KVB>;
-  auto kern = extend_mma_kernel<D, KVB, kQBf16>;
+  auto kern = extend_mma_kernel<D, KVB, kQBf16, kMasked>;
   static bool configured = false;
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
@@ -317,6 +344,15 @@ int extend_mma_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaSt
   }
   if (kvb == 2) return q_bf16 ? launch_mma<64, 2, true>(p, st) : launch_mma<64, 2, false>(p, st);
   return q_bf16 ? launch_mma<64, 1, true>(p, st) : launch_mma<64, 1, false>(p, st);
+}
+
+int extend_mma_masked_launch(const ExtendParams& p, int D, int kvb, bool q_bf16, cudaStream_t st) {
+  if (D == 128) {
+    if (kvb == 2) return q_bf16 ? launch_mma<128, 2, true, true>(p, st) : launch_mma<128, 2, false, true>(p, st);
+    return q_bf16 ? launch_mma<128, 1, true, true>(p, st) : launch_mma<128, 1, false, true>(p, st);
+  }
+  if (kvb == 2) return q_bf16 ? launch_mma<64, 2, true, true>(p, st) : launch_mma<64, 2, false, true>(p, st);
+  return q_bf16 ? launch_mma<64, 1, true, true>(p, st) : launch_mma<64, 1, false, true>(p, st);
 }
 
 }  // namespace b200attn

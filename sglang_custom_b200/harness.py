@@ -22,7 +22,8 @@ class Runner:
     """Drives the product path exactly as SGLang would: ModelRunner stand-in -> B200AttnBackend ->
     RadixAttention.forward -> backend.forward_decode / forward_extend -> C ABI."""
 
-    def __init__(self, case, device, max_reqs: Optional[int] = None):
+    def __init__(self, case, device, max_reqs: Optional[int] = None, sliding_window_size: Optional[int] = None,
+                 num_draft_tokens: Optional[int] = None):
         from sglang_custom_b200 import interfaces as itf
         from sglang_custom_b200.backend import B200AttnBackend
         self.itf = itf
@@ -37,10 +38,27 @@ class Runner:
         pool = self.mr.token_to_kv_pool
         pool.k_buffer[0].copy_(case.k_pool.to(device))
         pool.v_buffer[0].copy_(case.v_pool.to(device))
+        # sliding-window models (model_runner.sliding_window_size) / speculative decoding (server_args)
+        self.mr.sliding_window_size = sliding_window_size
+        self.mr.server_args.speculative_num_draft_tokens = num_draft_tokens
         self.backend = B200AttnBackend(self.mr)
         s = case.kv_scale if case.fp8 and case.kv_scale != 1.0 else None
         self.layer = itf.RadixAttention(num_heads=case.Hq, head_dim=case.D, scaling=case.sm_scale,
-                                        num_kv_heads=case.Hkv, layer_id=0, k_scale_float=s, v_scale_float=s)
+                                        num_kv_heads=case.Hkv, layer_id=0, k_scale_float=s, v_scale_float=s,
+                                        sliding_window_size=-1 if sliding_window_size is None else sliding_window_size)
+
+    def verify_batch(self, custom_mask: torch.Tensor):
+        """TARGET_VERIFY batch as EagleVerifyInput.prepare_for_verify leaves it (speculative/eagle_utils.py:255-276):
+        seq_lens = tokens already cached, the draft tokens' slots sit behind them in req_to_token, the mask comes in
+        spec_info.custom_mask.  The case must have extend_lens == num_draft_tokens for every request."""
+        itf, c, dev = self.itf, self.case, self.device
+        prefix = c.extend_prefix_lens.to(c.seq_lens.dtype)
+        return itf.ForwardBatch(
+            forward_mode=itf.ForwardMode.TARGET_VERIFY, batch_size=c.bs, req_pool_indices=c.req_pool_indices.to(dev),
+            seq_lens=prefix.to(dev), out_cache_loc=c.out_cache_loc.to(dev), seq_lens_sum=int(prefix.sum()),
+            req_to_token_pool=self.mr.req_to_token_pool, token_to_kv_pool=self.mr.token_to_kv_pool,
+            attn_backend=self.backend, seq_lens_cpu=prefix.cpu(),
+            spec_info=types.SimpleNamespace(custom_mask=custom_mask.to(dev), draft_token_num=c.max_extend_len))
 
     def batch(self, mode=None):
         itf, c, dev = self.itf, self.case, self.device
@@ -60,11 +78,11 @@ class Runner:
             fb.extend_num_tokens = c.T
         return fb
 
-    def forward(self, mode=None, save_kv_cache: bool = True, strided_qkv: bool = True) -> torch.Tensor:
+    def forward(self, mode=None, save_kv_cache: bool = True, strided_qkv: bool = True, fb=None) -> torch.Tensor:
         """One attention forward; q/k/v arrive as strided views of one qkv buffer, as in LlamaAttention
         (models/llama.py:182-193) and as the reference's CPU tests make them on purpose (test_decode.py:105-110)."""
         c, dev = self.case, self.device
-        fb = self.batch(mode)
+        fb = self.batch(mode) if fb is None else fb
         self.backend.init_forward_metadata(fb)
         if strided_qkv and c.T > 0:
             qkv = torch.cat([c.q.reshape(c.T, c.Hq * c.D), c.k_new.reshape(c.T, c.Hkv * c.D),

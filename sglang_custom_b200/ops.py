@@ -169,10 +169,18 @@ def decode_workspace_bytes(n_ctas: int, Hq: int, Dv: int) -> int:
     return _lib.load().b200attn_decode_workspace_bytes(int(n_ctas), int(Hq), int(Dv))
 
 
-def decode_plan(seq_lens: torch.Tensor, n_ctas: int, plan: torch.Tensor, min_units_per_cta: int = 4) -> None:
+def decode_plan(seq_lens: torch.Tensor, n_ctas: int, plan: torch.Tensor, min_units_per_cta: int = 4,
+                sliding_window_size: int = -1) -> None:
+    """sliding_window_size > -1: plan over the last min(L, window + 1) tokens of every request
+    (update_sliding_window_buffer, triton_backend.py:927-955); decode() then reads the window from the plan."""
     _cuda(seq_lens, plan)
     if plan.dtype != torch.int32 or not plan.is_contiguous():
         raise B200AttnError("decode_plan: plan must be a contiguous int32 tensor")
+    if sliding_window_size is not None and sliding_window_size > -1:
+        check(_lib.load().b200attn_decode_plan_window(
+            seq_lens.data_ptr(), _is_i64(seq_lens), seq_lens.numel(), int(n_ctas), int(min_units_per_cta),
+            int(sliding_window_size), plan.data_ptr(), plan.numel() * 4, _stream(plan)), "b200attn_decode_plan_window")
+        return
     check(_lib.load().b200attn_decode_plan(
         seq_lens.data_ptr(), _is_i64(seq_lens), seq_lens.numel(), int(n_ctas), int(min_units_per_cta),
         plan.data_ptr(), plan.numel() * 4, _stream(plan)), "b200attn_decode_plan")
@@ -243,8 +251,12 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            extend_seq_lens: torch.Tensor, extend_prefix_lens: torch.Tensor, extend_start_loc: torch.Tensor,
            max_extend_len: int, sm_scale: float, logit_cap: float = 0.0, k_scale: float = 1.0,
            v_scale: float = 1.0, causal: bool = True, kv_dtype: Optional[torch.dtype] = None,
-           impl: int = _lib.EXTEND_AUTO, lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """q,out [T,Hq,D]; see b200attn_extend in include/b200attn.h."""
+           impl: int = _lib.EXTEND_AUTO, lse_out: Optional[torch.Tensor] = None, sliding_window_size: int = -1,
+           custom_mask: Optional[torch.Tensor] = None, mask_indptr: Optional[torch.Tensor] = None,
+           skip_prefix_custom_mask: bool = True) -> torch.Tensor:
+    """q,out [T,Hq,D]; see b200attn_extend / b200attn_extend_masked in include/b200attn.h.
+    sliding_window_size / custom_mask / mask_indptr / skip_prefix_custom_mask carry the meaning they have in
+    extend_attention_fwd (triton_ops/extend_attention.py:306-324)."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, extend_seq_lens,
           extend_prefix_lens, extend_start_loc)
     T, Hq, D = q.shape
@@ -262,6 +274,27 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
         raise B200AttnError("extend: req_to_token must be int32 with contiguous rows")
     if req_pool_indices.dtype != seq_lens.dtype:
         raise B200AttnError("extend: req_pool_indices and seq_lens must share a dtype")
+    masked = custom_mask is not None or (sliding_window_size is not None and sliding_window_size > -1)
+    if masked:
+        if impl == _lib.EXTEND_TCGEN05:
+            raise B200AttnError("extend: the tcgen05 kernel has no sliding-window / custom-mask predicate")
+        if custom_mask is not None:
+            _cuda(custom_mask, mask_indptr)
+            if custom_mask.dtype not in (torch.bool, torch.uint8) or not custom_mask.is_contiguous():
+                raise B200AttnError("extend: custom_mask must be a contiguous bool/uint8 tensor")
+            if mask_indptr is None or mask_indptr.dtype != torch.int64 or mask_indptr.numel() < bs + 1 \
+                    or not mask_indptr.is_contiguous():
+                raise B200AttnError("extend: mask_indptr must be contiguous int64 [bs+1]")
+        check(_lib.load().b200attn_extend_masked(
+            q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+            k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+            seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
+            extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
+            _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
+            int(bool(causal)), int(sliding_window_size if sliding_window_size is not None else -1),
+            _ptr(custom_mask), _ptr(mask_indptr), int(bool(skip_prefix_custom_mask)), _ptr(lse_out), _stream(q)),
+            "b200attn_extend_masked")
+        return out
     check(_lib.load().b200attn_extend(
         q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
         k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
