@@ -20,6 +20,7 @@
  *                                sgl-kernel/csrc/attention/merge_attn_states.cu:32-106
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
  *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
+ *   b200attn_decode_multiq       cached-prefix part of TARGET_VERIFY batches (triton_backend.py:227-264)
  *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
  *   b200attn_extend_masked       triton_ops/extend_attention.py:158-175,236-247 (sliding window, custom mask)
  *   b200attn_flatten_kv_indices  layers/attention/utils.py:5-41 (create_flashinfer_kv_indices_triton)
@@ -187,6 +188,24 @@ int b200attn_decode_merge(void* out, int64_t out_tok_stride, int bs, int Hq, int
                           const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
                           float* lse_out, b200attn_stream_t stream);
 
+/* nq query tokens per request over the same seq_lens[i] keys, no mask among them: the cached-prefix part of a
+ * speculative-decoding verify batch (TARGET_VERIFY: every draft token sees the whole prefix, triton_backend.py:227-264,
+ * triton_ops/extend_attention.py stage 1 with SKIP_PREFIX_CUSTOM_MASK).  The nq * (Hq / Hkv) <= 16 rows of a kv head
+ * share one pass over K/V.  Arguments as b200attn_decode except
+ *   q   [bs, nq, Hq, D]: q_req_stride between requests, q_tok_stride between the nq tokens of a request (elements)
+ *   out [bs, nq, Hq, D]: out_req_stride / out_tok_stride likewise
+ *   lse_out (optional) fp32, element (i, t, h) at i * lse_req_stride + t * Hq + h
+ *   workspace: b200attn_decode_workspace_bytes(n_ctas, Hq * nq, D)
+ * The draft-token part (custom mask) is b200attn_extend_masked with
+ * sliding_window_size = B200ATTN_WINDOW_NEW_TOKENS_ONLY, combined by b200attn_merge_state. */
+int b200attn_decode_multiq(const void* q, int64_t q_req_stride, int64_t q_tok_stride, void* out,
+                           int64_t out_req_stride, int64_t out_tok_stride, const void* k_pool, const void* v_pool,
+                           int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride,
+                           const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs, int nq, int Hq,
+                           int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale, float logit_cap, float k_scale,
+                           float v_scale, const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
+                           float* lse_out, int64_t lse_req_stride, b200attn_stream_t stream);
+
 /* ---------------------------------------------------------------- 2-way LSE merge
  * out = (e^{la-m} a + e^{lb-m} b) / (e^{la-m} + e^{lb-m}),  lse = log(sum) + m, m = max(la, lb);
  * +inf LSE is treated as -inf (merge_attn_states.cu:47-50).
@@ -219,7 +238,8 @@ int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_
 /* Extend with the two extra predicates of TritonAttnBackend.forward_extend (triton_backend.py:658-684 ->
  * triton_ops/extend_attention.py:42-303): a sliding window and a speculative-decoding custom mask
  * (TARGET_VERIFY batches, triton_backend.py:227-264).  All other arguments as b200attn_extend.
- *   sliding_window_size  -1: none.  W >= 0: of the P_i cached-prefix keys only the last Wp = min(P_i, W + 1) are read
+ *   sliding_window_size  -1: none.  B200ATTN_WINDOW_NEW_TOKENS_ONLY (-2): no cached-prefix key at all -- the new-token
+ *                        part of a verify batch whose prefix part comes from b200attn_decode_multiq.  W >= 0: of the P_i cached-prefix keys only the last Wp = min(P_i, W + 1) are read
  *                        (window_kv_indices, triton_backend.py:299-309,927-955) and, for W > 0, the key at offset jw
  *                        in [0, Wp) of that range is visible to query t (0-based inside the request's new tokens)
  *                        iff t <= jw + W (extend_attention.py:168-174).  New-token keys keep the plain causal rule:
@@ -231,16 +251,19 @@ int b200attn_extend(const void* q, int64_t q_tok_stride, void* out, int64_t out_
  *                        default skip = True, extend_attention.py:322).  EAGLE tree masks are subsets of the causal
  *                        mask, for which this is exactly the reference's predicate.
  *   A query whose keys are all masked produces 0 (the reference's online softmax produces NaN there).
- * Served by the register-MMA kernel (verify batches are num_draft_tokens rows per request). */
+ * impl as in b200attn_extend: a custom mask is served by the register-MMA kernel only (verify batches are
+ * num_draft_tokens rows per request); a sliding window alone also by the tcgen05 kernel (AUTO picks it for
+ * max_extend_len >= 128, D == 128, causal, logit_cap == 0). */
 int b200attn_extend_masked(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
                            const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
                            const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
                            const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
                            const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
                            int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
-                           float logit_cap, float k_scale, float v_scale, int causal, int sliding_window_size,
+                           float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
                            const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask,
                            float* lse_out, b200attn_stream_t stream);
+#define B200ATTN_WINDOW_NEW_TOKENS_ONLY (-2)
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */
 #define B200ATTN_EXTEND_MMA 2     /* register-MMA kernel (short / ragged rows, FP8 KV, D == 64) */

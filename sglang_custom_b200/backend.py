@@ -77,6 +77,7 @@ class ForwardMetadata:
     total_lens: Optional[torch.Tensor] = None
     custom_mask: Optional[torch.Tensor] = None
     mask_indptr: Optional[torch.Tensor] = None
+    prefix_seq_lens: Optional[torch.Tensor] = None  # = forward_batch.seq_lens of a verify batch (its own dtype)
 
 
 class B200AttnBackend(AttentionBackend):
@@ -118,6 +119,7 @@ class B200AttnBackend(AttentionBackend):
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.scale_mode = _lib.SCALE_DIV
         self.writeback_scaled_kv = False
+        self.verify_via_decode = True  # TARGET_VERIFY: cached-prefix part on the split-KV decode kernel
         self.route_decode_tail = True  # MIXED batches: extend_len == 1 tail rows go to the decode kernel
 
     # ------------------------------------------------------------------ buffers
@@ -128,6 +130,11 @@ class B200AttnBackend(AttentionBackend):
         # second plan for sliding-window layers (the reference keeps window_kv_indptr / window_kv_indices beside
         # kv_indptr / kv_indices, triton_backend.py:124-135)
         self.window_plan = torch.zeros_like(self.plan) if self.sliding_window_size is not None else None
+        # TARGET_VERIFY: up to 16 (draft token, q head) rows of a kv head share one pass over the cached prefix
+        self.verify_workspace = None
+        if self.num_draft_tokens:
+            vws = ops.decode_workspace_bytes(self.n_ctas, self.num_kv_head * 16, self.v_head_dim)
+            self.verify_workspace = torch.empty(vws // 4, dtype=torch.float32, device=self.device)
 
     # ------------------------------------------------------------------ metadata
     def init_forward_metadata(self, forward_batch):
@@ -204,8 +211,11 @@ class B200AttnBackend(AttentionBackend):
             n = spec_info.custom_mask.numel()
             mask[:n] = spec_info.custom_mask.view(torch.uint8) if spec_info.custom_mask.dtype == torch.bool \
                 else spec_info.custom_mask
+        if bs > 0:
+            self._plan_decode(sl)  # the cached-prefix part runs on the split-KV decode kernel
         return ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=nd, extend_seq_lens=ext,
-                               extend_prefix_lens=prefix, total_lens=total, custom_mask=mask, mask_indptr=mask_indptr)
+                               extend_prefix_lens=prefix, total_lens=total, custom_mask=mask, mask_indptr=mask_indptr,
+                               prefix_seq_lens=sl)
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -341,7 +351,31 @@ class B200AttnBackend(AttentionBackend):
             if window > -1:  # the reference has no window in spec inference either (triton_backend.py:228)
                 raise NotImplementedError("b200 attention backend: sliding window with speculative decoding")
             rpi = md.req_pool_indices if md.req_pool_indices is not None else forward_batch.req_pool_indices
-            ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi[:md.bs], md.total_lens,
+            rpi = rpi[:md.bs]
+            nd, Hq = md.max_extend_len, layer.tp_q_head_num
+            per_pass = 16 // (Hq // layer.tp_k_head_num) if Hq // layer.tp_k_head_num <= 16 else 0
+            if self.verify_via_decode and causal and per_pass > 0 and -(-nd // per_pass) <= 4 \
+                    and self.verify_workspace is not None and o3.is_contiguous():
+                # HBM-bound like decode: every draft token sees the whole cached prefix, so that part is ONE
+                # split-KV pass per 16 (token, head) rows over the page table (b200attn_decode_multiq); the few
+                # draft-token keys take the tree mask in the register-MMA kernel; an LSE merge joins the two.
+                q4, o4 = q3.unflatten(0, (md.bs, nd)), o3.unflatten(0, (md.bs, nd))
+                lse_p = torch.empty((md.bs, nd, Hq), dtype=torch.float32, device=q.device)
+                for t0 in range(0, nd, per_pass):
+                    ops.decode_multiq(q4[:, t0:t0 + per_pass], o4[:, t0:t0 + per_pass], pool.k_buffer[lid],
+                                      pool.v_buffer[lid], table, rpi, md.prefix_seq_lens, self.plan, self.n_ctas,
+                                      self.verify_workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype,
+                                      lse_out=lse_p[:, t0:t0 + per_pass])
+                o_d = torch.empty_like(o3)
+                lse_d = torch.empty((md.bs * nd, Hq), dtype=torch.float32, device=q.device)
+                ops.extend(q3, o_d, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
+                           md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, nd, layer.scaling, cap,
+                           k_scale, v_scale, causal=True, kv_dtype=pool.dtype, lse_out=lse_d,
+                           sliding_window_size=_lib.WINDOW_NEW_TOKENS_ONLY, custom_mask=md.custom_mask,
+                           mask_indptr=md.mask_indptr)
+                ops.merge_state(o3, lse_p.view(md.bs * nd, Hq), o_d, lse_d, out=o3)
+                return o
+            ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
                        md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, md.max_extend_len,
                        layer.scaling, cap, k_scale, v_scale, causal=causal, kv_dtype=pool.dtype,
                        custom_mask=md.custom_mask, mask_indptr=md.mask_indptr)

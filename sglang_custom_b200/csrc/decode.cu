@@ -45,6 +45,11 @@ struct DecodeParams {
   int64_t q_tok_stride, out_tok_stride, pool_tok_stride, table_stride;
   int idx_is_i64;
   int bs, Hq, Hkv, G;
+  // multi-query rows (b200attn_decode_multiq): the G = nq * Gr MMA rows of a kv head are nq query tokens x Gr q heads
+  // that share the request's keys.  Row r -> token r / Gr, q head kv_head * Gr + r % Gr.  Plain decode: nq = 1, Gr = G.
+  int Gr, Hq_real;
+  int64_t q_sub_stride, out_sub_stride;  // stride between the nq tokens of a request (elements)
+  int64_t lse_req_stride;                // lse_out: [request][token][Hq_real]
   int n_ctas;
   float scale_log2;  // sm_scale * k_scale * log2(e)   (logit_cap == 0)
   float scale_raw;   // sm_scale * k_scale
@@ -264,9 +269,11 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
         // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
         uint32_t qa[KSTEPS][4];
         {
-          const uint16_t* qrow0 = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride +
-                                  static_cast<int64_t>(kv_head * G + row) * D;
-          const uint16_t* qrow1 = qrow0 + 8 * D;
+          const uint16_t* qb = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride;
+          const int Gr = p.Gr;
+          const uint16_t* qrow0 = qb + (row / Gr) * p.q_sub_stride + static_cast<int64_t>(kv_head * Gr + row % Gr) * D;
+          const uint16_t* qrow1 = qb + ((row + 8) / Gr) * p.q_sub_stride +
+                                  static_cast<int64_t>(kv_head * Gr + (row + 8) % Gr) * D;
           const bool v0 = row < G, v1 = !kG8 && (row + 8 < G);
   #pragma unroll
           for (int ks = 0; ks < KSTEPS; ++ks) {
@@ -508,10 +515,11 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
             const float m = rr ? m1 : m0, l = rr ? l1 : l0;
             const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
             const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
-            const int head = kv_head * G + r;
+            const int head = kv_head * G + r;  // workspace index (virtual head)
+            const int sub = r / p.Gr, head_real = kv_head * p.Gr + r % p.Gr;
             if (seg.slot < 0) {
               uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
-                              static_cast<int64_t>(head) * D;
+                              sub * p.out_sub_stride + static_cast<int64_t>(head_real) * D;
               if constexpr (!kFp8) {
   #pragma unroll
                 for (int nb = 0; nb < NBLK; ++nb)
@@ -525,7 +533,8 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
                   *reinterpret_cast<uint2*>(dst + c * 16 + 4 * qd) = make_uint2(w0, w1);
                 }
               }
-              if (p.lse_out != nullptr && qd == 0) p.lse_out[static_cast<int64_t>(seg.batch) * p.Hq + head] = lse;
+              if (p.lse_out != nullptr && qd == 0)
+                p.lse_out[static_cast<int64_t>(seg.batch) * p.lse_req_stride + sub * p.Hq_real + head_real] = lse;
             } else {
               float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D;
               if constexpr (!kFp8) {
@@ -563,12 +572,16 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
   const int W = plan[kPlanUnitsPerCta];
   const int32_t* cum = plan + kPlanHeader;
   const int c0 = cum[i], c1 = cum[i + 1];
-  uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + static_cast<int64_t>(head) * D;
+  const int kvh = head / p.G, r = head % p.G;  // virtual head -> (token, real q head), see DecodeParams
+  const int sub = r / p.Gr, head_real = kvh * p.Gr + r % p.Gr;
+  uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + sub * p.out_sub_stride +
+                  static_cast<int64_t>(head_real) * D;
+  float* lse_dst = p.lse_out ? p.lse_out + static_cast<int64_t>(i) * p.lse_req_stride + sub * p.Hq_real + head_real : nullptr;
   constexpr int EPL = D / 32;  // elements per lane
   if (c1 == c0) {  // empty request: defined as zeros
 #pragma unroll
     for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
-    if (p.lse_out != nullptr && lane == 0) p.lse_out[static_cast<int64_t>(i) * p.Hq + head] = -INFINITY;
+    if (lse_dst != nullptr && lane == 0) *lse_dst = -INFINITY;
     return;
   }
   const int cta0 = c0 / W, cta1 = (c1 - 1) / W;
@@ -601,8 +614,7 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
 #pragma unroll
   for (int e = 0; e < EPL; e += 2)
     *reinterpret_cast<uint32_t*>(dst + lane * EPL + e) = pack2<kBf16>(acc[e] * inv, acc[e + 1] * inv);
-  if (p.lse_out != nullptr && lane == 0)
-    p.lse_out[static_cast<int64_t>(i) * p.Hq + head] = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
+  if (lse_dst != nullptr && lane == 0) *lse_dst = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -690,6 +702,7 @@ static int decode_setup(DecodeParams& p, const void* q, int64_t q_tok_stride, vo
   p.pool_tok_stride = pool_tok_stride; p.table_stride = table_stride;
   p.idx_is_i64 = idx_is_i64;
   p.bs = bs; p.Hq = Hq; p.Hkv = Hkv; p.G = G;
+  p.Gr = G; p.Hq_real = Hq; p.q_sub_stride = 0; p.out_sub_stride = 0; p.lse_req_stride = Hq;
   p.n_ctas = n_ctas;
   p.scale_raw = sm_scale * k_scale;
   p.scale_log2 = sm_scale * k_scale * kLog2e;
@@ -770,4 +783,36 @@ extern "C" B2_EXPORT int b200attn_decode_merge(void* out, int64_t out_tok_stride
                               workspace, workspace_bytes, lse_out, false);
   if (rc != B200ATTN_OK) return rc;
   return launch_merge(p, D, q_dtype == B200ATTN_BF16, static_cast<cudaStream_t>(stream));
+}
+
+// nq query tokens per request over the SAME seq_lens[i] keys, no mask among them: the cached-prefix part of a
+// speculative-decoding verify batch (TARGET_VERIFY, triton_backend.py:227-264), where every draft token sees the whole
+// prefix.  The nq * G rows of a kv head ride the MMA row dimension the GQA group already uses, so K/V are streamed from
+// HBM once for all of them (nq * Hq / Hkv <= 16).  The caller merges the draft-token part with b200attn_merge_state.
+extern "C" B2_EXPORT int b200attn_decode_multiq(
+    const void* q, int64_t q_req_stride, int64_t q_tok_stride, void* out, int64_t out_req_stride, int64_t out_tok_stride,
+    const void* k_pool, const void* v_pool, int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride,
+    const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs, int nq, int Hq, int Hkv, int D,
+    int q_dtype, int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale, const int32_t* plan,
+    int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out, int64_t lse_req_stride,
+    b200attn_stream_t stream) {
+  if (bs == 0 || nq == 0) return B200ATTN_OK;
+  B2_REQUIRE(nq > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && nq * (Hq / Hkv) <= 16, B200ATTN_ERR_UNSUPPORTED,
+             "decode_multiq: nq * Hq / Hkv = %d * %d / %d must be <= 16", nq, Hq, Hkv);
+  B2_REQUIRE(q_tok_stride % 8 == 0 && out_tok_stride % 8 == 0, B200ATTN_ERR_INVALID,
+             "decode_multiq: token strides must be multiples of 8 elements");
+  DecodeParams p;
+  const int rc = decode_setup(p, q, q_req_stride, out, out_req_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
+                              table_stride, req_pool_indices, seq_lens, idx_is_i64, bs, Hq * nq, Hkv, D, q_dtype,
+                              kv_dtype, sm_scale, logit_cap, k_scale, v_scale, plan, n_ctas, workspace,
+                              workspace_bytes, lse_out, true);
+  if (rc != B200ATTN_OK) return rc;
+  p.Gr = Hq / Hkv; p.Hq_real = Hq;
+  p.q_sub_stride = q_tok_stride; p.out_sub_stride = out_tok_stride;
+  p.lse_req_stride = lse_req_stride;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool q_bf16 = q_dtype == B200ATTN_BF16;
+  const int rc2 = launch_partial(p, D, elem_size(kv_dtype), q_bf16, st);
+  if (rc2 != B200ATTN_OK) return rc2;
+  return launch_merge(p, D, q_bf16, st);
 }

@@ -64,15 +64,25 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool q_bf16 = q_dtype == B200ATTN_BF16;
-  if (window >= 0 || custom_mask != nullptr) {
-    // the predicate lives in the register-MMA kernel only (verify batches are a few rows per request)
-    B2_REQUIRE(impl != B200ATTN_EXTEND_TCGEN05, B200ATTN_ERR_UNSUPPORTED,
-               "extend: the tcgen05 kernel has no sliding-window / custom-mask predicate");
-    B2_REQUIRE(custom_mask == nullptr || mask_indptr != nullptr, B200ATTN_ERR_INVALID,
-               "extend: custom_mask without mask_indptr");
+  const bool tc_ok = extend_tc_supported(p, D, kvb);
+  if (window == B200ATTN_WINDOW_NEW_TOKENS_ONLY) {
+    B2_REQUIRE(impl != B200ATTN_EXTEND_TCGEN05, B200ATTN_ERR_UNSUPPORTED, "extend: new-tokens-only runs on the register-MMA kernel");
     return extend_mma_masked_launch(p, D, kvb, q_bf16, st);
   }
-  const bool tc_ok = extend_tc_supported(p, D, kvb);
+  if (window >= 0 || custom_mask != nullptr) {
+    // the custom mask lives in the register-MMA kernel only (verify batches are a few rows per request); the
+    // sliding window is a per-row key range, which the tcgen05 kernel handles too
+    B2_REQUIRE(custom_mask == nullptr || mask_indptr != nullptr, B200ATTN_ERR_INVALID,
+               "extend: custom_mask without mask_indptr");
+    const bool tc_win = tc_ok && custom_mask == nullptr && causal != 0;
+    if (impl == B200ATTN_EXTEND_TCGEN05) {
+      B2_REQUIRE(tc_win, B200ATTN_ERR_UNSUPPORTED,
+                 "extend: the tcgen05 kernel takes a sliding window (D == 128, causal, logit_cap == 0) but no custom mask");
+      return extend_tc_launch(p, q_bf16, kvb, st);
+    }
+    if (impl == B200ATTN_EXTEND_AUTO && tc_win && max_extend_len >= 128) return extend_tc_launch(p, q_bf16, kvb, st);
+    return extend_mma_masked_launch(p, D, kvb, q_bf16, st);
+  }
   if (impl == B200ATTN_EXTEND_TCGEN05) {
     B2_REQUIRE(tc_ok, B200ATTN_ERR_UNSUPPORTED,
                "extend: the tcgen05 kernel needs D == 128 and logit_cap == 0 (D=%d kv bytes=%d cap=%g)", D,
@@ -108,13 +118,14 @@ extern "C" B2_EXPORT int b200attn_extend_masked(
     int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
     const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
     const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,
-    float sm_scale, float logit_cap, float k_scale, float v_scale, int causal, int sliding_window_size,
+    float sm_scale, float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
     const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask, float* lse_out,
     b200attn_stream_t stream) {
-  B2_REQUIRE(sliding_window_size >= -1, B200ATTN_ERR_INVALID, "extend_masked: sliding_window_size=%d", sliding_window_size);
+  B2_REQUIRE(sliding_window_size >= B200ATTN_WINDOW_NEW_TOKENS_ONLY, B200ATTN_ERR_INVALID,
+             "extend_masked: sliding_window_size=%d", sliding_window_size);
   return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
                      table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
                      extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
-                     k_scale, v_scale, causal, B200ATTN_EXTEND_MMA, lse_out, sliding_window_size, custom_mask,
+                     k_scale, v_scale, causal, impl, lse_out, sliding_window_size, custom_mask,
                      mask_indptr, skip_prefix_custom_mask, stream);
 }

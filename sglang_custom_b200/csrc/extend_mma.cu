@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(kExtThreads) extend_mma_kernel(const ExtendPar
   int kv_begin = 0;
   if constexpr (kMasked) {
     if (p.window >= 0) kv_begin = P - min(P, p.window + 1);
+    else if (p.window == B200ATTN_WINDOW_NEW_TOKENS_ONLY) kv_begin = P;  // prefix part computed elsewhere
   }
   const int tile0 = kv_begin / BN;
 

@@ -90,10 +90,14 @@ struct Prof<false> {
 // One K/V tile of one query row: S (fp32, tensor memory) -> online-softmax update -> P (bf16, tensor memory).
 //   kMask: some of the 128 keys are invisible to some row (diagonal / last tile) -> mask, MUFU only
 //   kEmu : of every 4 element pairs, kEmu take the FMA-pipe exp2
-template <bool kBf16, bool kMask, int kEmu, bool kProf>
+//   kWin : sliding-window variant -- keys [0, nlo) of the tile are invisible too, and a row may see nothing at all
+//          in its first tiles: the running maximum then stays -inf until the first visible key (no rescale needed,
+//          l and O are still exact zeros)
+template <bool kBf16, bool kMask, int kEmu, bool kProf, bool kWin = false>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const uint32_t bar_s,
                                              const uint32_t bar_p, const int j, const int nvis,
-                                             const float scale_log2, float& m_used, float& l, Prof<kProf>& prof) {
+                                             const float scale_log2, float& m_used, float& l, Prof<kProf>& prof,
+                                             const int nlo = 0) {
   ptx::mbar_wait(bar_s, j & 1);
   ptx::tc_fence_after();
   prof.mark(0);
@@ -105,7 +109,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 
   if constexpr (kMask) {
 #pragma unroll
-    for (int i = 0; i < 128; ++i) s[i] = (i < nvis) ? s[i] : 0xff800000u;  // -inf
+    for (int i = 0; i < 128; ++i) s[i] = (i < nvis && (!kWin || i >= nlo)) ? s[i] : 0xff800000u;  // -inf
   }
   float mx8[8];
 #pragma unroll
@@ -121,14 +125,14 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   prof.mark(2);
 
   if (j == 0) {
-    m_used = (mx == -INFINITY) ? 0.f : mx;
+    m_used = (!kWin && mx == -INFINITY) ? 0.f : mx;
   } else {
     const bool grow = mx > m_used + kRescaleThreshold;
     if (__any_sync(0xffffffffu, grow)) {
       // S_t(j) is complete, so PV_t(j-1) -- issued before it -- is complete too: O_t is stable until this
       // thread group hands P_t(j) to the MMA warp
       const float m_new = grow ? mx : m_used;
-      const float f = fast_exp2(m_used - m_new);
+      const float f = (kWin && !grow) ? 1.f : fast_exp2(m_used - m_new);  // kWin: m_used may still be -inf
       l *= f;
       m_used = m_new;
 #pragma unroll
@@ -145,7 +149,8 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   }
   prof.mark(3);
 
-  const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_used, -m_used);
+  const float m_sub = (kWin && kMask && m_used == -INFINITY) ? 0.f : m_used;  // nothing seen yet: every P is exp2(-inf) = 0
+  const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_sub, -m_sub);
   float2 sum2[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
@@ -177,7 +182,9 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 // the way into shared memory (F2FP.F16.E4M3.UNPACK_B, exact; it issues on the ALU pipe and overlaps the MUFU
 // exponentials -- scripts/ubench/pipes.cu), so the MMA runs in f16 and kBf16 is false.  kQCvt: q/out are bf16 while
 // the MMA runs in f16 (bf16 model over an FP8 KV cache): Q is converted on its way into shared memory.
-template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false>
+// kWin: sliding-window layers (p.window >= 0, semantics in extend.cuh): the K/V walk starts at the 128-key tile that
+// holds the first prefix key inside the window, and the first tiles carry a per-row lower bound.
+template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false, bool kWin = false>
 __global__ void __launch_bounds__(kThreads, 1)
 extend_tc_kernel(const ExtendParams p, const int pair_heads) {
   static_assert(!(kFp8 && kBf16) && !(kQCvt && kBf16), "FP8 KV runs the MMA in f16");
@@ -212,8 +219,15 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
   int kv_end[2], nt[2];
   kv_end[0] = p.causal ? min(L, P + min(q0[0] + kTile, E)) : L;
   kv_end[1] = valid1 ? (p.causal ? min(L, P + min(q0[1] + kTile, E)) : L) : 0;
-  nt[0] = (kv_end[0] + kTile - 1) / kTile;
-  nt[1] = (kv_end[1] + kTile - 1) / kTile;
+  // sliding window: first prefix key inside the window, and the tile-aligned key the walk starts at (tile j of this
+  // CTA covers keys [kv_base + 128 j, kv_base + 128 (j + 1)))
+  int kv_begin = 0, kv_base = 0;
+  if constexpr (kWin) {
+    kv_begin = P - min(P, p.window + 1);
+    kv_base = kv_begin & ~(kTile - 1);
+  }
+  nt[0] = (kv_end[0] - kv_base + kTile - 1) / kTile;
+  nt[1] = valid1 ? (kv_end[1] - kv_base + kTile - 1) / kTile : 0;
   const int n = max(nt[0], nt[1]);
   const int kv_len = max(kv_end[0], kv_end[1]);
 
@@ -286,17 +300,34 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
       const int lim_row0 = p.causal ? min(P + q0[t] + 1, L) : L;                     // the tile's smallest limit
       float m_used = 0.f, l = 0.f;
       const int my_n = nt[t];
-      const int n_unmasked = min(my_n, lim_row0 / kTile);  // tiles every row of this Q tile sees completely
+      const int n_unmasked = min(my_n, (lim_row0 - kv_base) / kTile);  // tiles every row of this Q tile sees completely
       const uint32_t bar_s = bar(S_FULL + t), bar_p = bar(P_FULL + 2 * t);
+      // window: prefix keys below lo are invisible to this row (new-token keys, >= P, have no lower bound); the
+      // first n_lead tiles hold such a key for some row of the Q tile
+      int lo = 0, n_lead = 0;
+      if constexpr (kWin) {
+        const int tq = q0[t] + row;
+        lo = (p.window > 0 ? min(kv_begin + max(0, tq - p.window), P) : kv_begin) - kv_base;
+        const int lo_max = (p.window > 0 ? min(kv_begin + max(0, q0[t] + kTile - 1 - p.window), P) : kv_begin) - kv_base;
+        n_lead = min(my_n, (lo_max + kTile - 1) / kTile);
+      }
+      const int lim_rel = lim - kv_base;
 
       prof.begin();
       int j = 0;
+      if constexpr (kWin) {
+#pragma unroll 1
+        for (; j < n_lead; ++j)
+          softmax_tile<kBf16, true, kEmu, kProf, true>(tS, tO, bar_s, bar_p, j, lim_rel - j * kTile, p.scale_log2, m_used,
+                                                       l, prof, lo - j * kTile);
+      }
 #pragma unroll 1
       for (; j < n_unmasked; ++j)
-        softmax_tile<kBf16, false, kEmu, kProf>(tS, tO, bar_s, bar_p, j, kTile, p.scale_log2, m_used, l, prof);
+        softmax_tile<kBf16, false, kEmu, kProf, kWin>(tS, tO, bar_s, bar_p, j, kTile, p.scale_log2, m_used, l, prof);
 #pragma unroll 1
       for (; j < my_n; ++j)
-        softmax_tile<kBf16, true, kEmu, kProf>(tS, tO, bar_s, bar_p, j, lim - j * kTile, p.scale_log2, m_used, l, prof);
+        softmax_tile<kBf16, true, kEmu, kProf, kWin>(tS, tO, bar_s, bar_p, j, lim_rel - j * kTile, p.scale_log2, m_used, l,
+                                                     prof, lo - j * kTile);
 
       // ---- epilogue: O_t / l -> global
       ptx::mbar_wait(bar(O_FULL + t), 0);
@@ -448,7 +479,7 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         const int m = pw + 3 * (4 * c + (lane >> 3));
-        const int tok = j * kTile + 8 * m + (lane & 7);
+        const int tok = kv_base + j * kTile + 8 * m + (lane & 7);
         sreg[c] = (m < 16 && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
       }
     };
@@ -608,7 +639,14 @@ KernelFn pick_kernel(int emu, bool prof) {
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
   const int emu = (p.exp_emu >= 0 && p.exp_emu <= 3) ? p.exp_emu : 2;
   KernelFn kern;
-  if (kvb == 1)  // FP8-E4M3 pool: f16 MMA, e4m3 expanded by the producers; bf16 q converted on load
+  if (p.window >= 0) {
+    if (kvb == 1)
+      kern = q_bf16 ? tc::extend_tc_kernel<false, 0, false, true, true, true>
+                    : tc::extend_tc_kernel<false, 0, false, true, false, true>;
+    else
+      kern = q_bf16 ? tc::extend_tc_kernel<true, 0, false, false, false, true>
+                    : tc::extend_tc_kernel<false, 0, false, false, false, true>;
+  } else if (kvb == 1)  // FP8-E4M3 pool: f16 MMA, e4m3 expanded by the producers; bf16 q converted on load
     kern = q_bf16 ? tc::extend_tc_kernel<false, 0, false, true, true> : tc::extend_tc_kernel<false, 0, false, true, false>;
   else
     kern = q_bf16 ? pick_kernel<true>(emu, p.prof != nullptr) : pick_kernel<false>(emu, p.prof != nullptr);

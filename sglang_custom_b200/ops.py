@@ -225,6 +225,37 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
     return out
 
 
+def decode_multiq(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+                  req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                  plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
+                  k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
+                  lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q,out [bs,nq,Hq,D] (any request / token strides, head stride D); every one of the nq tokens of request i attends
+    to keys [0, seq_lens[i]) -- see b200attn_decode_multiq.  lse_out: fp32 [bs,nq,Hq] (request stride free)."""
+    _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, workspace, lse_out)
+    bs, nq, Hq, D = q.shape
+    Hkv = k_pool.shape[1]
+    if out.shape != q.shape or out.dtype != q.dtype:
+        raise B200AttnError("decode_multiq: out must match q")
+    if q.stride(3) != 1 or q.stride(2) != D or out.stride(3) != 1 or out.stride(2) != D:
+        raise B200AttnError("decode_multiq: q/out head stride must be D")
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise B200AttnError("decode_multiq: req_to_token must be int32 with contiguous rows")
+    if req_pool_indices.dtype != seq_lens.dtype:
+        raise B200AttnError("decode_multiq: req_pool_indices and seq_lens must share a dtype")
+    if lse_out is not None and (lse_out.dtype != torch.float32 or lse_out.shape != (bs, nq, Hq)
+                                or lse_out.stride(2) != 1 or lse_out.stride(1) != Hq):
+        raise B200AttnError("decode_multiq: lse_out must be fp32 [bs,nq,Hq] with contiguous (token, head)")
+    check(_lib.load().b200attn_decode_multiq(
+        q.data_ptr(), q.stride(0), q.stride(1), out.data_ptr(), out.stride(0), out.stride(1), k_pool.data_ptr(),
+        v_pool.data_ptr(), k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
+        req_pool_indices.data_ptr(), seq_lens.data_ptr(), _is_i64(seq_lens), bs, nq, Hq, Hkv, D, _dt(q.dtype),
+        _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
+        plan.data_ptr(), int(n_ctas), workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+        _ptr(lse_out), lse_out.stride(0) if lse_out is not None else 0, _stream(q)), "b200attn_decode_multiq")
+    return out
+
+
 def merge_state(a: torch.Tensor, lse_a: torch.Tensor, b: torch.Tensor, lse_b: torch.Tensor,
                 out: Optional[torch.Tensor] = None, out_lse: Optional[torch.Tensor] = None):
     """merge_state / merge_state_v2 (layers/attention/merge_state.py:26-46)."""
@@ -276,8 +307,6 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
         raise B200AttnError("extend: req_pool_indices and seq_lens must share a dtype")
     masked = custom_mask is not None or (sliding_window_size is not None and sliding_window_size > -1)
     if masked:
-        if impl == _lib.EXTEND_TCGEN05:
-            raise B200AttnError("extend: the tcgen05 kernel has no sliding-window / custom-mask predicate")
         if custom_mask is not None:
             _cuda(custom_mask, mask_indptr)
             if custom_mask.dtype not in (torch.bool, torch.uint8) or not custom_mask.is_contiguous():
@@ -291,7 +320,7 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
             seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
             extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
             _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
-            int(bool(causal)), int(sliding_window_size if sliding_window_size is not None else -1),
+            int(bool(causal)), int(impl), int(sliding_window_size if sliding_window_size is not None else -1),
             _ptr(custom_mask), _ptr(mask_indptr), int(bool(skip_prefix_custom_mask)), _ptr(lse_out), _stream(q)),
             "b200attn_extend_masked")
         return out

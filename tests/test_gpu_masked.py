@@ -34,14 +34,15 @@ def _as16(fx):
     return fx, True
 
 
-def _direct_extend(case, device, kp, vp, window=-1, mask=None, indptr=None, skip=True, causal=True, logit_cap=0.0):
+def _direct_extend(case, device, kp, vp, window=-1, mask=None, indptr=None, skip=True, causal=True, logit_cap=0.0,
+                   impl=_lib.EXTEND_AUTO):
     c = H.to_device(case, device)
     out = torch.empty_like(c.q)
     s = case.kv_scale if case.fp8 else 1.0
     ops.extend(c.q, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens,
                c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
                logit_cap, s, s, causal=causal, kv_dtype=torch.float8_e4m3fn if case.fp8 else None,
-               sliding_window_size=window, custom_mask=None if mask is None else mask.to(device),
+               impl=impl, sliding_window_size=window, custom_mask=None if mask is None else mask.to(device),
                mask_indptr=None if indptr is None else indptr.to(device), skip_prefix_custom_mask=skip)
     torch.cuda.synchronize(device)
     return out
@@ -218,13 +219,16 @@ VERIFY = [
 ]
 
 
+@pytest.mark.parametrize("via_decode", [True, False])
 @pytest.mark.parametrize("bs,Hq,Hkv,D,prefix,nd,kw", VERIFY)
-def test_target_verify_backend_vs_oracle(bs, Hq, Hkv, D, prefix, nd, kw, device):
+def test_target_verify_backend_vs_oracle(bs, Hq, Hkv, D, prefix, nd, kw, via_decode, device):
     lens = [p + nd for p in prefix]
     case = synth.make_case(bs, Hq, Hkv, D, lens, extend_lens=[nd] * bs, seed=6000 + nd, **kw)
     kp, vp = H.pool_after_write(case)
     mask, indptr = _tree_masks(case, 6100 + nd)
     r = H.Runner(case, device, num_draft_tokens=nd)
+    # both routes: prefix part on the split-KV decode kernel + masked draft part + LSE merge, or one masked extend
+    r.backend.verify_via_decode = via_decode
     out = r.forward(fb=r.verify_batch(mask))
     dk, dv = r.pools()
     assert H.pools_equal(dk, kp) and H.pools_equal(dv, vp), "KV write of the draft tokens must be bit-exact"
@@ -309,8 +313,15 @@ def test_causal_mask_equals_no_mask_bitwise(device):
     assert torch.equal(plain, masked)
     masked_all = _direct_extend(case, device, kp, vp, -1, mask, indptr, skip=False)
     assert torch.equal(plain, masked_all)
-    wide = _direct_extend(case, device, kp, vp, 1 << 20)
+    wide = _direct_extend(case, device, kp, vp, 1 << 20, impl=_lib.EXTEND_MMA)
     assert torch.equal(plain, wide)
+    # the tcgen05 kernel's window variant with a window wider than every prefix == its plain variant
+    plain_tc = torch.empty_like(c.q)
+    ops.extend(c.q, plain_tc, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens,
+               c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
+               impl=_lib.EXTEND_TCGEN05)
+    wide_tc = _direct_extend(case, device, kp, vp, 1 << 20, impl=_lib.EXTEND_TCGEN05)
+    assert torch.equal(plain_tc, wide_tc)
     H.assert_close(plain, H.oracle_extend(case, kp, vp), what="vs torch_native")
 
 
@@ -342,7 +353,7 @@ def test_prefix_mask_noncausal_and_fully_masked_rows(device):
     H.assert_close(out, want, what="window + mask")
 
 
-def test_masked_extend_rejects_tcgen05_and_bad_args(device):
+def test_masked_extend_rejects_bad_args(device):
     case = synth.make_case(1, 8, 2, 128, [300], extend_lens=[200], seed=85)
     kp, vp = H.pool_after_write(case)
     c = H.to_device(case, device)
@@ -350,7 +361,8 @@ def test_masked_extend_rejects_tcgen05_and_bad_args(device):
     with pytest.raises(_lib.B200AttnError):
         ops.extend(c.q, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens,
                    c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
-                   impl=_lib.EXTEND_TCGEN05, sliding_window_size=10)
+                   impl=_lib.EXTEND_TCGEN05, custom_mask=torch.ones(200 * 300, dtype=torch.bool, device=device),
+                   mask_indptr=torch.tensor([0, 60000], dtype=torch.int64, device=device))
     with pytest.raises(_lib.B200AttnError):
         ops.extend(c.q, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens,
                    c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
@@ -359,3 +371,74 @@ def test_masked_extend_rejects_tcgen05_and_bad_args(device):
     r.layer.sliding_window_size = 64
     with pytest.raises(_lib.B200AttnError):
         r.forward()
+
+
+# ------------------------------------------------------------------ sliding window on the tcgen05 kernel
+TC_WINDOW = [
+    # bs, Hq, Hkv, D, seq_lens, extend_lens, window, kwargs
+    (2, 4, 2, 128, [3000, 1500], [1500, 700], 300, {}),          # window start mid-tile, rows with no visible prefix
+    (2, 4, 2, 128, [2100, 900], [600, 900], 1000, {}),           # several fully visible prefix tiles
+    (2, 3, 1, 128, [1300, 400], [300, 130], 127, {}),            # odd GQA group: two q tiles of one head per CTA
+    (2, 4, 1, 128, [1500, 777], [520, 129], 200, {"fp8": True, "kv_scale": 0.1135}),
+    (1, 4, 2, 128, [1029], [900], 0, {}),                        # window 0: one prefix key, no window mask
+    (2, 8, 2, 128, [640, 384], [256, 128], 64, {"page_size": 16, "dtype": torch.float16}),
+]
+
+
+@pytest.mark.parametrize("bs,Hq,Hkv,D,lens,ext,W,kw", TC_WINDOW)
+def test_window_extend_tcgen05_vs_oracle_and_mma(bs, Hq, Hkv, D, lens, ext, W, kw, device):
+    case = synth.make_case(bs, Hq, Hkv, D, lens, extend_lens=ext, seed=7000 + W, **kw)
+    kp, vp = H.pool_after_write(case)
+    tc = _direct_extend(case, device, kp, vp, W, impl=_lib.EXTEND_TCGEN05)
+    mma = _direct_extend(case, device, kp, vp, W, impl=_lib.EXTEND_MMA)
+    ok, ov = _oracle_pools(case, kp, vp)
+    want = tm.extend(case.q, ok, ov, case.req_to_token, case.req_pool_indices, case.seq_lens, case.extend_prefix_lens,
+                     case.extend_seq_lens, case.sm_scale, True, W)
+    H.assert_close(tc, want, what="tcgen05 window vs oracle")
+    H.assert_close(mma, want, what="register-MMA window vs oracle")
+    H.assert_close(tc, mma, 8e-3, 8e-4, what="tcgen05 vs register-MMA")
+
+
+# ------------------------------------------------------------------ several query tokens per request on the decode kernel
+@pytest.mark.parametrize("bs,Hq,Hkv,D,lens,nq,kw", [
+    (5, 32, 8, 128, [3000, 0, 64, 513, 17], 4, {}),
+    (3, 8, 1, 128, [2000, 333, 100], 2, {"fp8": True, "kv_scale": 0.1135}),
+    (3, 8, 2, 64, [300, 200, 100], 3, {}),
+    (2, 4, 4, 128, [50, 257], 16, {"dtype": torch.float16}),
+    (4, 16, 2, 128, [900, 2, 64, 1500], 2, {"idx_dtype": torch.int32, "page_size": 16}),
+])
+def test_decode_multiq_vs_oracle(bs, Hq, Hkv, D, lens, nq, kw, device):
+    """nq query tokens per request over the same keys == nq independent decode calls (oracle: torch_native decode),
+    with the LSE of every (request, token, head); split-invariant."""
+    case = synth.make_case(bs, Hq, Hkv, D, [max(x, 1) for x in lens], seed=8000 + nq, **kw)
+    kp, vp = case.k_pool, case.v_pool  # no KV write: the keys are the pool as it is
+    g = torch.Generator().manual_seed(1)
+    q = torch.randn((bs, nq, Hq, D), generator=g).to(case.dtype)
+    seq = torch.tensor(lens, dtype=case.seq_lens.dtype)
+    ok, ov = _oracle_pools(case, kp, vp)
+    want = torch.stack([H.tn.decode(q[:, t].contiguous(), ok, ov, case.req_to_token, case.req_pool_indices, seq,
+                                    case.sm_scale) for t in range(nq)], 1)
+    for i, L in enumerate(lens):
+        if L == 0:
+            want[i] = 0  # empty request: defined as zeros, LSE -inf
+    c = H.to_device(case, device)
+    s = case.kv_scale if case.fp8 else 1.0
+    outs = []
+    for n_ctas in (148, 2):
+        plan = torch.zeros(ops.decode_plan_bytes(bs, n_ctas) // 4, dtype=torch.int32, device=device)
+        ws = torch.empty(ops.decode_workspace_bytes(n_ctas, Hq * nq, D) // 4, dtype=torch.float32, device=device)
+        ops.decode_plan(seq.to(device), n_ctas, plan, 1)
+        qd = q.to(device)
+        out = torch.full_like(qd, float("nan"))
+        lse = torch.full((bs, nq, Hq), float("nan"), dtype=torch.float32, device=device)
+        ops.decode_multiq(qd, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, seq.to(device), plan,
+                          n_ctas, ws, case.sm_scale, 0.0, s, s, kv_dtype=torch.float8_e4m3fn if case.fp8 else None,
+                          lse_out=lse)
+        torch.cuda.synchronize(device)
+        H.assert_close(out, want, what=f"decode_multiq n_ctas={n_ctas}")
+        for i, L in enumerate(lens):
+            assert bool(torch.isinf(lse[i]).all()) == (L == 0)
+        outs.append((out, lse))
+    H.assert_close(outs[0][0], outs[1][0], 4e-3, 4e-4, what="split invariance")
+    fin = torch.isfinite(outs[0][1])
+    assert float((outs[0][1][fin] - outs[1][1][fin]).abs().max()) < 1e-3
