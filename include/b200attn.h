@@ -267,6 +267,8 @@ int b200attn_extend_masked(const void* q, int64_t q_tok_stride, void* out, int64
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */
 #define B200ATTN_EXTEND_MMA 2     /* register-MMA kernel (short / ragged rows, FP8 KV, D == 64) */
+#define B200ATTN_EXTEND_TCGEN05_STEP64 3 /* tcgen05 kernel with S double-buffered in 64-key steps (extend_tc64.cu);
+                                            measured ~equal / slightly slower than TCGEN05 at C3, kept for comparison */
 
 /* ---------------------------------------------------------------- page-table utilities
  * kv_indices[kv_indptr[i] + j] = req_to_token[req_pool_indices[i], kv_start[i] + j], j < lens[i]

@@ -1,0 +1,645 @@
+// Paged extend / prefill attention on the 5th-generation tensor cores, 64-key-step variant (B200ATTN_EXTEND_TCGEN05,
+// selected by extend_tc_launch unless B200ATTN_EXTEND_TC=1).
+//
+// Same roles, shared-memory layout, producers and semantics as extend_tc.cu (read its header first).  What changes is
+// the hand-off between the MMA warp and the softmax warpgroups.  In extend_tc.cu S_t (128 keys) and P_t share ONE
+// tensor-memory buffer per Q tile, so S_t(j+1) = Q K^T can only be issued after softmax(j) has finished and P_t(j) V
+// has been issued: per Q tile the loop is the serial chain softmax -> PV -> QK -> softmax, measured 3 540 cycles per
+// 128-key tile against 2 048 tensor cycles (clock64 phase profile, profiles/README.md) -- the tensor pipe idles 40 %.
+// Here the 128 S columns of a Q tile are two 64-key buffers.  Step i (64 keys) lives in buffer i & 1: while the softmax
+// warps work on step i, Q K^T of step i + 1 is already complete in the other buffer and step i + 2 is issued as soon as
+// P(i) V is -- the chain is broken, the softmax warps never wait for S.  Cost: Q K^T becomes an M128 N64 SS-mode MMA,
+// which is shared-memory-operand bound (48 instead of 32 cycles per k-step, scripts/ubench/umma.cu), so the tensor
+// work per 128 keys and Q-tile pair is 2 560 cycles instead of 2 048.
+//   tensor memory: S_t buffer h at column 128 t + 64 h (P(step) over its first 32 columns), O_t at 256 + 128 t
+//   the lazy O rescale now needs PV(i-1) complete, which S(i) no longer implies: the MMA warp commits every PV to
+//   PV_DONE(t, h) and a softmax thread group waits on it only in the (rare) steps that rescale.
+#include "extend.cuh"
+#include "tc_ptx.cuh"
+
+namespace b200attn {
+namespace tc64 {
+
+constexpr int kThreads = 384;       // 3 warpgroups
+constexpr int kProducerWarps = 3;
+// setmaxnreg targets.  The CTA is launched with 168 registers per thread (64 512 in its pool), so the 128 threads of the
+// third warpgroup must release at least what the 256 softmax threads claim: 128 x (168 - 88) = 256 x (208 - 168).
+constexpr int kRegsSoftmax = 208;
+constexpr int kRegsOther = 88;
+constexpr int kTile = 128;           // BM = BN = D = 128
+constexpr int kTileBytes = 32768;    // 128 rows x 256 B
+constexpr int kHalfBytes = 16384;    // 128 rows x 128 B (one 64-element swizzle atom column)
+constexpr int kOffQ = 0;             // Q0, Q1
+constexpr int kOffK = 2 * kTileBytes;
+constexpr int kOffV = 4 * kTileBytes;
+constexpr int kOffBar = 6 * kTileBytes;
+constexpr int kSmemBytes = kOffBar + 32 * 8 + 16 + 1024;  // + barriers + tmem slot + alignment slack
+constexpr float kRescaleThreshold = 8.0f;                 // log2 units
+
+// S_FULL + 2 * t + h: S of a step in buffer h of Q tile t is complete; P_FULL + 2 * t + h: its P is in tensor memory;
+// PV_DONE + 2 * t + h: the PV that consumed it has finished
+enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 3, V_FULL = 5, V_EMPTY = 7, S_FULL = 9, O_FULL = 13, P_FULL = 15, PV_DONE = 19, kNumBars = 23 };
+constexpr int kStep = 64;  // keys per softmax / MMA hand-off step
+
+// dev-only phase timing (kernel variant kProf): every warp accumulates clock64 deltas, CTA (0,0,0) stores them
+template <bool kOn>
+struct Prof {
+  unsigned long long acc[8];
+  long long t0;
+  __device__ __forceinline__ void begin() {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0;
+    t0 = clock64();
+  }
+  __device__ __forceinline__ void mark(int slot) {
+    const long long now = clock64();
+    acc[slot] += static_cast<unsigned long long>(now - t0);
+    t0 = now;
+  }
+  __device__ __forceinline__ void flush(unsigned long long* dst, int warp, int lane) {
+    if (dst != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+      for (int i = 0; i < 8; ++i) dst[warp * 8 + i] = acc[i];
+  }
+};
+template <>
+struct Prof<false> {
+  __device__ __forceinline__ void begin() {}
+  __device__ __forceinline__ void mark(int) {}
+  __device__ __forceinline__ void flush(unsigned long long*, int, int) {}
+};
+
+// One 64-key step of one query row: S (fp32, tensor memory) -> online-softmax update -> P (bf16, tensor memory).
+//   kMask: some of the 64 keys are invisible to some row (diagonal / last / window-start step) -> mask, MUFU only
+//   kEmu : of every 4 element pairs, kEmu take the FMA-pipe exp2
+//   kWin : sliding-window variant -- keys [0, nlo) of the step are invisible too, and a row may see nothing at all in
+//          its first steps: the running maximum then stays -inf until the first visible key
+//   i    : step index of this Q tile (buffer i & 1, barrier phase (i >> 1) & 1)
+template <bool kBf16, bool kMask, int kEmu, bool kProf, bool kWin = false>
+__device__ __forceinline__ void softmax_step(const uint32_t tS_t, const uint32_t tO, const uint32_t bar_s_t,
+                                             const uint32_t bar_p_t, const uint32_t bar_pv_t, const int i,
+                                             const int nvis, const float scale_log2, float& m_used, float& l,
+                                             Prof<kProf>& prof, const int nlo = 0) {
+  const uint32_t h = static_cast<uint32_t>(i & 1);
+  const uint32_t tS = tS_t + 64u * h;
+  ptx::mbar_wait(bar_s_t + 8u * h, (i >> 1) & 1);
+  ptx::tc_fence_after();
+  prof.mark(0);
+  uint32_t s[64];
+  ptx::tmem_ld32(tS, s);
+  ptx::tmem_ld32(tS + 32, s + 32);
+  ptx::tmem_wait_ld();
+  prof.mark(1);
+
+  if constexpr (kMask) {
+#pragma unroll
+    for (int e = 0; e < 64; ++e) s[e] = (e < nvis && (!kWin || e >= nlo)) ? s[e] : 0xff800000u;  // -inf
+  }
+  float mx8[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) mx8[e] = fmaxf(__uint_as_float(s[e]), __uint_as_float(s[8 + e]));
+#pragma unroll
+  for (int e = 16; e < 64; e += 16)
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      mx8[k] = fmaxf(fmaxf(mx8[k], __uint_as_float(s[e + k])), __uint_as_float(s[e + 8 + k]));
+  float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
+                   fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
+  mx *= scale_log2;  // scale > 0: the maximum commutes with the scaling
+  prof.mark(2);
+
+  if (i == 0) {
+    m_used = (!kWin && mx == -INFINITY) ? 0.f : mx;
+  } else {
+    const bool grow = mx > m_used + kRescaleThreshold;
+    if (__any_sync(0xffffffffu, grow)) {
+      // O_t must be stable: PV(i-1) -- issued when P(i-1) was handed over, possibly still running -- has to be complete;
+      // PV(i) cannot start before this thread group hands P(i) over
+      ptx::mbar_wait(bar_pv_t + 8u * static_cast<uint32_t>((i - 1) & 1), ((i - 1) >> 1) & 1);
+      ptx::tc_fence_after();
+      const float m_new = grow ? mx : m_used;
+      const float f = (kWin && !grow) ? 1.f : fast_exp2(m_used - m_new);  // kWin: m_used may still be -inf
+      l *= f;
+      m_used = m_new;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        ptx::tmem_ld32(tO + c * 32, o);
+        ptx::tmem_wait_ld();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
+        ptx::tmem_st32(tO + c * 32, o);
+      }
+      ptx::tmem_wait_st();
+    }
+  }
+  prof.mark(3);
+
+  const float m_sub = (kWin && kMask && m_used == -INFINITY) ? 0.f : m_used;  // nothing seen yet: every P is exp2(-inf) = 0
+  const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_sub, -m_sub);
+  float2 sum2[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+  uint32_t pk[32];
+#pragma unroll
+  for (int e2 = 0; e2 < 32; ++e2) {
+    const int e = 2 * e2;
+    float2 x = ptx::ffma2(make_float2(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), sc2, nm2);
+    if (!kMask && (e2 & 3) < kEmu) {
+      x = ptx::exp2_poly2(x);
+    } else {
+      x.x = fast_exp2(x.x);
+      x.y = fast_exp2(x.y);
+    }
+    sum2[e2 & 3] = ptx::fadd2(sum2[e2 & 3], x);
+    pk[e2] = pack2<kBf16>(x.x, x.y);
+  }
+  ptx::tmem_st32(tS, pk);
+  ptx::tmem_wait_st();
+  ptx::tc_fence_before();
+  ptx::mbar_arrive(bar_p_t + 8u * h);
+  const float2 st = ptx::fadd2(ptx::fadd2(sum2[0], sum2[1]), ptx::fadd2(sum2[2], sum2[3]));
+  l += st.x + st.y;
+  prof.mark(4);
+}
+
+// kBf16: MMA operand format (bf16 or f16).  kFp8: the pool holds e4m3 bytes; the producers expand them to f16 on
+// the way into shared memory (F2FP.F16.E4M3.UNPACK_B, exact; it issues on the ALU pipe and overlaps the MUFU
+// exponentials -- scripts/ubench/pipes.cu), so the MMA runs in f16 and kBf16 is false.  kQCvt: q/out are bf16 while
+// the MMA runs in f16 (bf16 model over an FP8 KV cache): Q is converted on its way into shared memory.
+// kWin: sliding-window layers (p.window >= 0, semantics in extend.cuh): the K/V walk starts at the 128-key tile that
+// holds the first prefix key inside the window, and the first tiles carry a per-row lower bound.
+template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false, bool kWin = false>
+__global__ void __launch_bounds__(kThreads, 1)
+extend_tc64_kernel(const ExtendParams p, const int pair_heads) {
+  static_assert(!(kFp8 && kBf16) && !(kQCvt && kBf16), "FP8 KV runs the MMA in f16");
+  constexpr bool kOutBf16 = kBf16 || kQCvt;  // dtype of q and out in global memory
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms repeat every 1024 B
+  const uint32_t bars = smem + kOffBar;
+  auto bar = [&](int i) { return bars + 8u * static_cast<uint32_t>(i); };
+  const uint32_t tmem_slot = bars + 32 * 8;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  Prof<kProf> prof;
+  const int req = p.grid_order ? blockIdx.z : blockIdx.y;
+  const int E = p.extend_seq_lens[req];
+  // heavy (late) tiles first
+  const int zt = p.grid_order ? static_cast<int>(gridDim.y) - 1 - static_cast<int>(blockIdx.y)
+                              : static_cast<int>(gridDim.z) - 1 - static_cast<int>(blockIdx.z);
+  int head[2], q0[2];
+  if (pair_heads) {
+    head[0] = 2 * blockIdx.x; head[1] = head[0] + 1;
+    q0[0] = q0[1] = zt * kTile;
+  } else {
+    head[0] = head[1] = blockIdx.x;
+    q0[0] = 2 * zt * kTile; q0[1] = q0[0] + kTile;
+  }
+  if (q0[0] >= E) return;  // CTA-uniform, before any barrier or allocation
+  const bool valid1 = q0[1] < E;
+  const int P = p.extend_prefix_lens[req];
+  const int L = static_cast<int>(load_index(p.seq_lens, p.idx_is_i64, req));
+  const int start = p.extend_start_loc[req];
+  const int kv_head = head[0] / p.G;
+  int kv_end[2], nt[2];
+  kv_end[0] = p.causal ? min(L, P + min(q0[0] + kTile, E)) : L;
+  kv_end[1] = valid1 ? (p.causal ? min(L, P + min(q0[1] + kTile, E)) : L) : 0;
+  // sliding window: first prefix key inside the window, and the tile-aligned key the walk starts at (tile j of this
+  // CTA covers keys [kv_base + 128 j, kv_base + 128 (j + 1)))
+  int kv_begin = 0, kv_base = 0;
+  if constexpr (kWin) {
+    kv_begin = P - min(P, p.window + 1);
+    kv_base = kv_begin & ~(kTile - 1);
+  }
+  nt[0] = (kv_end[0] - kv_base + kTile - 1) / kTile;
+  nt[1] = valid1 ? (kv_end[1] - kv_base + kTile - 1) / kTile : 0;
+  const int n = max(nt[0], nt[1]);
+  const int kv_len = max(kv_end[0], kv_end[1]);
+  // 64-key steps of each Q tile (tile j of the K/V ring = steps 2 j and 2 j + 1)
+  int ns[2];
+  ns[0] = (kv_end[0] - kv_base + kStep - 1) / kStep;
+  ns[1] = valid1 ? (kv_end[1] - kv_base + kStep - 1) / kStep : 0;
+  const int n_steps = max(ns[0], ns[1]);
+
+  // ---------------------------------------------------------------- setup
+  if (warp == 8) ptx::tmem_alloc<512>(tmem_slot);
+  if (tid == 0) {
+    ptx::mbar_init(bar(Q_FULL), 256);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(bar(K_FULL + i), kProducerWarps * 32);
+      ptx::mbar_init(bar(K_EMPTY + i), 1);
+      ptx::mbar_init(bar(V_FULL + i), kProducerWarps * 32);
+      ptx::mbar_init(bar(V_EMPTY + i), 1);
+      ptx::mbar_init(bar(O_FULL + i), 1);
+      for (int h = 0; h < 2; ++h) {
+        ptx::mbar_init(bar(S_FULL + 2 * i + h), 1);
+        ptx::mbar_init(bar(P_FULL + 2 * i + h), 128);
+        ptx::mbar_init(bar(PV_DONE + 2 * i + h), 1);
+      }
+    }
+    ptx::fence_mbar_init();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp < 8) {
+    ptx::setmaxnreg_inc<kRegsSoftmax>();
+    // ================================================================ softmax + output of Q tile t
+    const int t = warp >> 2;
+    const int wq = warp & 3;          // tensor-memory lane quarter of this warp
+    const int row = wq * 32 + lane;   // query row of this thread inside the tile
+    const int tix = tid - 128 * t;
+    const bool tile_valid = (t == 0) || valid1;
+
+    // ---- Q tile -> shared memory, K-major 128B-swizzle layout (two 64-element column halves)
+    {
+      const uint16_t* qbase = reinterpret_cast<const uint16_t*>(p.q) + static_cast<int64_t>(head[t]) * kTile;
+      const uint32_t sq = smem + kOffQ + t * kTileBytes;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const int id = tix + 128 * c;
+        const int r = id >> 4, ch = id & 15;
+        const bool ok = tile_valid && (q0[t] + r < E);
+        const uint16_t* src = ok ? qbase + static_cast<int64_t>(start + q0[t] + r) * p.q_tok_stride + ch * 8
+                                 : reinterpret_cast<const uint16_t*>(p.q);
+        const uint32_t dst = sq + (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
+        if constexpr (kQCvt) {
+          uint4 w = ok ? __ldg(reinterpret_cast<const uint4*>(src)) : make_uint4(0u, 0u, 0u, 0u);
+          w.x = ptx::bf16x2_to_f16x2(w.x); w.y = ptx::bf16x2_to_f16x2(w.y);
+          w.z = ptx::bf16x2_to_f16x2(w.z); w.w = ptx::bf16x2_to_f16x2(w.w);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w) : "memory");
+        } else {
+          cp_async16(dst, src, ok ? 16 : 0);
+        }
+      }
+      if constexpr (!kQCvt) {
+        cp_async_commit();
+        cp_async_wait<0>();
+      }
+      ptx::fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
+      ptx::mbar_arrive(bar(Q_FULL));
+    }
+
+    if (tile_valid) {
+      const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(wq * 32) << 16);
+      const uint32_t tS = lane_base + t * 128;        // S_t, and P_t over its first 64 columns
+      const uint32_t tO = lane_base + 256 + t * 128;  // O_t
+      const bool row_valid = q0[t] + row < E;
+      const int lim = row_valid ? (p.causal ? min(P + q0[t] + row + 1, L) : L) : L;  // keys visible to this row
+      const int lim_row0 = p.causal ? min(P + q0[t] + 1, L) : L;                     // the tile's smallest limit
+      float m_used = 0.f, l = 0.f;
+      const int my_n = ns[t];
+      const int n_unmasked = min(my_n, (lim_row0 - kv_base) / kStep);  // steps every row of this Q tile sees completely
+      const uint32_t bar_s = bar(S_FULL + 2 * t), bar_p = bar(P_FULL + 2 * t), bar_pv = bar(PV_DONE + 2 * t);
+      // window: prefix keys below lo are invisible to this row (new-token keys, >= P, have no lower bound); the
+      // first n_lead steps hold such a key for some row of the Q tile
+      int lo = 0, n_lead = 0;
+      if constexpr (kWin) {
+        const int tq = q0[t] + row;
+        lo = (p.window > 0 ? min(kv_begin + max(0, tq - p.window), P) : kv_begin) - kv_base;
+        const int lo_max = (p.window > 0 ? min(kv_begin + max(0, q0[t] + kTile - 1 - p.window), P) : kv_begin) - kv_base;
+        n_lead = min(my_n, (lo_max + kStep - 1) / kStep);
+      }
+      const int lim_rel = lim - kv_base;
+
+      prof.begin();
+      int j = 0;
+      if constexpr (kWin) {
+#pragma unroll 1
+        for (; j < n_lead; ++j)
+          softmax_step<kBf16, true, kEmu, kProf, true>(tS, tO, bar_s, bar_p, bar_pv, j, lim_rel - j * kStep, p.scale_log2,
+                                                       m_used, l, prof, lo - j * kStep);
+      }
+#pragma unroll 1
+      for (; j < n_unmasked; ++j)
+        softmax_step<kBf16, false, kEmu, kProf, kWin>(tS, tO, bar_s, bar_p, bar_pv, j, kStep, p.scale_log2, m_used, l, prof);
+#pragma unroll 1
+      for (; j < my_n; ++j)
+        softmax_step<kBf16, true, kEmu, kProf, kWin>(tS, tO, bar_s, bar_p, bar_pv, j, lim_rel - j * kStep, p.scale_log2,
+                                                     m_used, l, prof, lo - j * kStep);
+
+      // ---- epilogue: O_t / l -> global
+      ptx::mbar_wait(bar(O_FULL + t), 0);
+      ptx::tc_fence_after();
+      prof.mark(5);
+      const float inv = l > 0.f ? p.v_scale / l : 0.f;
+      uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) +
+                      static_cast<int64_t>(start + q0[t] + row) * p.out_tok_stride + static_cast<int64_t>(head[t]) * kTile;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        ptx::tmem_ld32(tO + c * 32, o);
+        ptx::tmem_wait_ld();
+        if (row_valid) {
+#pragma unroll
+          for (int v4 = 0; v4 < 4; ++v4) {
+            uint4 w;
+            w.x = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 0]) * inv, __uint_as_float(o[8 * v4 + 1]) * inv);
+            w.y = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 2]) * inv, __uint_as_float(o[8 * v4 + 3]) * inv);
+            w.z = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 4]) * inv, __uint_as_float(o[8 * v4 + 5]) * inv);
+            w.w = pack2<kOutBf16>(__uint_as_float(o[8 * v4 + 6]) * inv, __uint_as_float(o[8 * v4 + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + v4 * 8) = w;
+          }
+        }
+      }
+      if (p.lse_out != nullptr && row_valid)
+        p.lse_out[static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] =
+            l > 0.f ? (m_used + log2f(l)) * kLn2 : -INFINITY;
+      prof.mark(6);
+      prof.flush(p.prof, warp, lane);
+      ptx::tc_fence_before();
+    }
+  } else if (warp == 8) {
+    ptx::setmaxnreg_dec<kRegsOther>();
+    // ================================================================ MMA issuer
+    // The whole warp walks the loop (mbarrier waits included) so that every operand stays warp-uniform; one
+    // elected lane -- the same one throughout, tcgen05.commit tracks the MMAs of the issuing thread -- issues.
+    const bool leader = ptx::elect_one();
+    constexpr int kFmt = kBf16 ? 1 : 0;
+    constexpr uint32_t idesc_qk = ptx::instr_desc_f16(kFmt, 128, kStep, 0);  // A = Q, B = 64 rows of K: both K-major
+    constexpr uint32_t idesc_pv = ptx::instr_desc_f16(kFmt, 128, 128, 1);    // A = P (tmem), B = V: MN-major
+    // K-major SW128: 8-row groups 1024 B apart; a 16-element k step is 32 B inside the 128 B atom row,
+    // the second 64-element half of D lives in the next 16 KiB sub-tile; the keys of an odd step start 64 rows
+    // (8192 B) into each sub-tile.
+    // MN-major SW128 (V: rows = keys = the contraction index, 128 B of D per row): 8-key groups 1024 B apart
+    // (SBO), the two 64-element halves of D 16 KiB apart (LBO); a 16-key k step is 2048 B.
+    const uint64_t qd0 = ptx::smem_desc_sw128(smem + kOffQ, 16, 1024);
+    const uint64_t kd0 = ptx::smem_desc_sw128(smem + kOffK, 16, 1024);
+    const uint64_t vd0 = ptx::smem_desc_sw128(smem + kOffV, kHalfBytes, 1024);
+    constexpr uint64_t kTileStep = kTileBytes >> 4;  // descriptor address units of 16 B
+
+    // S of step i of Q tile t: keys 64 (i & 1) .. of K ring buffer (i >> 1) & 1 -> S buffer i & 1
+    auto issue_qk = [&](int t, int i) {
+      const int h = i & 1, kb = (i >> 1) & 1;
+      const uint64_t qd = qd0 + static_cast<uint64_t>(t) * kTileStep;
+      const uint64_t kd = kd0 + static_cast<uint64_t>(kb) * kTileStep + static_cast<uint64_t>(h) * ((kStep * 128) >> 4);
+      const uint32_t d = tmem_base + t * 128 + h * kStep;
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint64_t off = static_cast<uint64_t>(((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4);
+          ptx::umma_ss(d, qd + off, kd + off, idesc_qk, kk > 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(bar(S_FULL + 2 * t + h));
+      }
+      __syncwarp();
+    };
+    // O_t += P(step i) V: four k-steps (64 keys) of V ring buffer (i >> 1) & 1
+    auto issue_pv = [&](int t, int i) {
+      const int h = i & 1, vb = (i >> 1) & 1;
+      const uint64_t vd = vd0 + static_cast<uint64_t>(vb) * kTileStep + static_cast<uint64_t>(h) * ((4 * 2048) >> 4);
+      const uint32_t d = tmem_base + 256 + t * 128;
+      const uint32_t a = tmem_base + t * 128 + h * kStep;
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          ptx::umma_ts(d, a + kk * 8, vd + static_cast<uint64_t>((kk * 2048) >> 4), idesc_pv, (i > 0 || kk > 0) ? 1u : 0u);
+        ptx::umma_commit(bar(PV_DONE + 2 * t + h));
+      }
+      __syncwarp();
+    };
+    auto commit = [&](int b) {
+      if (leader) ptx::umma_commit(bar(b));
+      __syncwarp();
+    };
+
+    prof.begin();
+    ptx::mbar_wait(bar(Q_FULL), 0);
+    ptx::mbar_wait(bar(K_FULL + 0), 0);
+    ptx::fence_proxy_async();  // K/V arrive through cp.async (generic proxy); the tensor core reads through the async proxy
+    ptx::tc_fence_after();
+    prof.mark(0);
+    // steps 0 and 1 (both S buffers) of both Q tiles: the softmax warps start with a full step of S in reserve
+    for (int i = 0; i < 2; ++i)
+      for (int t = 0; t < 2; ++t)
+        if (i < ns[t]) issue_qk(t, i);
+    commit(K_EMPTY + 0);
+    prof.mark(7);
+
+    int k_tile_ready = 0;  // highest K ring tile whose K_FULL has been waited for
+#pragma unroll 1
+    for (int i = 0; i < n_steps; ++i) {
+      const int j = i >> 1, vb = j & 1;
+      if ((i & 1) == 0) {  // first step of K/V tile j: its V rows
+        ptx::mbar_wait(bar(V_FULL + vb), (j >> 1) & 1);
+        ptx::fence_proxy_async();
+        prof.mark(3);
+      }
+      const int jn = (i + 2) >> 1;  // K tile of step i + 2
+      if (i + 2 < n_steps && jn > k_tile_ready) {
+        ptx::mbar_wait(bar(K_FULL + (jn & 1)), (jn >> 1) & 1);
+        ptx::fence_proxy_async();
+        k_tile_ready = jn;
+        prof.mark(4);
+      }
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (i < ns[t]) {
+          ptx::mbar_wait(bar(P_FULL + 2 * t + (i & 1)), (i >> 1) & 1);
+          prof.mark(1 + t);
+          ptx::tc_fence_after();
+          issue_pv(t, i);
+          if (i == ns[t] - 1) commit(O_FULL + t);
+          // the buffer P(i) sat in is free once that PV has run (the tensor pipe executes in issue order)
+          if (i + 2 < ns[t]) issue_qk(t, i + 2);
+          prof.mark(7);
+        }
+      }
+      if (i & 1) {
+        commit(V_EMPTY + vb);                               // both steps of V tile j have been issued
+        if (i + 1 < n_steps) commit(K_EMPTY + ((j + 1) & 1));  // so have both steps (i + 1, i + 2) of K tile j + 1
+      }
+    }
+    prof.flush(p.prof, warp, lane);
+  } else {
+    ptx::setmaxnreg_dec<kRegsOther>();
+    // ================================================================ producers: gather K/V rows through the page table
+    // A warp instruction copies two pool rows of this kv head (2 x 256 B, 16 lanes x 16 B each).  The 128 rows of a
+    // tile are 16 groups of 8 (one swizzle period); producer warp pw owns groups m = pw, pw + 3, ... and walks a
+    // group as four row pairs q, so the swizzled destination of (group k', pair q) is base_q + k' * 3072: four
+    // loop-invariant registers instead of one per copy.
+    const int pw = warp - 9;
+    const int32_t* trow = p.req_to_token + load_index(p.req_pool_indices, p.idx_is_i64, req) * p.table_stride;
+    constexpr int kGroups = 6;                       // groups per producer warp (the last one only for pw == 0)
+    // Page-table slots: lane i of load c holds the slot of row 8 * (pw + 3 * (4 c + i / 8)) + i % 8 -- the rows of
+    // this warp only, two coalesced-by-eight loads per tile, fetched one tile ahead.
+    int sreg[2];
+    auto load_slots = [&](int j) {
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int m = pw + 3 * (4 * c + (lane >> 3));
+        const int tok = kv_base + j * kTile + 8 * m + (lane & 7);
+        sreg[c] = (m < 16 && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
+      }
+    };
+    if constexpr (!kFp8) {
+      const int64_t row_bytes = p.pool_tok_stride * 2;
+      const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+      const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
+      const int sub = lane >> 4;                       // which row of the pair
+      const int ch = lane & 15;                        // 16-byte chunk of the 256-byte row
+      uint32_t dst_q[4];                               // destination of (group pw, pair q) relative to the tile base
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int r = 8 * pw + 2 * q + sub;
+        dst_q[q] = (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
+      }
+      // the copy of (group k', pair q) takes its slot from lane 8 * (k' % 4) + 2 q + sub of register k' / 4
+      int slot[4 * kGroups];
+      auto spread_slots = [&]() {
+#pragma unroll
+        for (int kq = 0; kq < 4 * kGroups; ++kq) {
+          const int kp = kq >> 2, q = kq & 3;
+          slot[kq] = __shfl_sync(0xffffffffu, sreg[kp >> 2], 8 * (kp & 3) + 2 * q + sub);
+        }
+      };
+      auto gather = [&](const uint8_t* base, uint32_t tile) {
+#pragma unroll
+        for (int kq = 0; kq < 4 * kGroups; ++kq) {
+          const int kp = kq >> 2, q = kq & 3;
+          if (pw + 3 * kp < 16)  // warp-uniform
+            cp_async16(tile + dst_q[q] + kp * 3072, base + static_cast<int64_t>(slot[kq]) * row_bytes);
+        }
+      };
+      load_slots(0);
+      prof.begin();
+#pragma unroll 1
+      for (int j = 0; j < n; ++j) {
+        const int b = j & 1, u = j >> 1;
+        spread_slots();
+        if (j + 1 < n) load_slots(j + 1);  // issued before this tile's copies so that it never queues behind them
+        prof.mark(0);
+        // K_j
+        ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
+        prof.mark(1);
+        gather(kbase, smem + kOffK + b * kTileBytes);
+        ptx::cp_async_mbar_arrive_noinc(bar(K_FULL + b));
+        prof.mark(2);
+        // V_j
+        ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
+        prof.mark(3);
+        gather(vbase, smem + kOffV + b * kTileBytes);
+        ptx::cp_async_mbar_arrive_noinc(bar(V_FULL + b));
+        prof.mark(4);
+      }
+    } else {
+      // FP8-E4M3 pool: a row of one kv head is 128 bytes; a warp instruction loads four rows (8 lanes x 16 B each),
+      // every lane expands its 16 e4m3 values to 16 f16 (two 16-byte chunks of the 256-byte shared-memory row) and
+      // stores them into the same UMMA canonical 128B-swizzle layout the 16-bit path fills with LDGSTS.  The loads of
+      // a half tile (three 8-row groups = six warp loads) are all issued before the first conversion.  Register
+      // stores go through the generic proxy: fence.proxy.async, then a plain mbarrier arrive.
+      const int64_t row_bytes = p.pool_tok_stride;
+      const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * kTile + (lane & 7) * 16;
+      const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * kTile + (lane & 7) * 16;
+      const int sub = lane >> 3;                       // which row of the quad
+      const int c0 = 2 * (lane & 7);                   // first of the two 16-byte f16 chunks this lane produces
+      uint32_t dst_q[2];                               // destination of (group pw, quad q), chunk c0; chunk c0+1 is ^ 16
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int r = 8 * pw + 4 * q + sub;
+        dst_q[q] = (c0 >> 3) * kHalfBytes + r * 128 + (((c0 & 7) ^ (r & 7)) << 4);
+      }
+      int scur[2];  // this tile's slots (sreg holds the next tile's); spread by shuffle at the point of use
+      // the twelve warp loads of a tile share are issued before the wait for the empty buffer: registers do not
+      // depend on shared memory, so the L2 / HBM latency overlaps the MMAs still reading the previous tile
+      auto issue_loads = [&](const uint8_t* base, uint4 (&w)[12]) {
+#pragma unroll
+        for (int kq = 0; kq < 12; ++kq) {
+          const int kp = kq >> 1;
+          if (pw + 3 * kp < 16) {  // warp-uniform
+            const int sl = __shfl_sync(0xffffffffu, scur[kp >> 2], 8 * (kp & 3) + 4 * (kq & 1) + sub);
+            w[kq] = ld_nc_16(base + static_cast<int64_t>(sl) * row_bytes);
+          }
+        }
+      };
+      auto expand_store = [&](uint32_t tile, const uint4 (&w)[12]) {
+#pragma unroll
+        for (int kq = 0; kq < 12; ++kq) {
+          const int kp = kq >> 1, q = kq & 1;
+          if (pw + 3 * kp < 16) {
+            const uint32_t d = tile + dst_q[q] + kp * 3072;
+            const uint32_t in[4] = {w[kq].x, w[kq].y, w[kq].z, w[kq].w};
+            uint32_t o[8];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              o[2 * e] = e4m3x2_to_f16x2(static_cast<uint16_t>(in[e] & 0xffffu));
+              o[2 * e + 1] = e4m3x2_to_f16x2(static_cast<uint16_t>(in[e] >> 16));
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(d), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(d ^ 16u), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
+          }
+        }
+      };
+      load_slots(0);
+      prof.begin();
+      uint4 w[12];
+      scur[0] = sreg[0]; scur[1] = sreg[1];
+      if (n > 0) issue_loads(kbase, w);
+#pragma unroll 1
+      for (int j = 0; j < n; ++j) {
+        const int b = j & 1, u = j >> 1;
+        if (j + 1 < n) load_slots(j + 1);
+        ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
+        expand_store(smem + kOffK + b * kTileBytes, w);
+        issue_loads(vbase, w);  // V_j on its way while K_j is published
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(bar(K_FULL + b));
+        ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
+        expand_store(smem + kOffV + b * kTileBytes, w);
+        scur[0] = sreg[0]; scur[1] = sreg[1];
+        if (j + 1 < n) issue_loads(kbase, w);  // K_{j+1}
+        ptx::fence_proxy_async();
+        ptx::mbar_arrive(bar(V_FULL + b));
+      }
+    }
+    prof.flush(p.prof, warp, lane);
+  }
+
+  // ---------------------------------------------------------------- teardown
+  __syncthreads();
+  if (warp == 8) {
+    __syncwarp();
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<512>(tmem_base);
+  }
+}
+
+}  // namespace tc64
+
+namespace {
+using KernelFn = void (*)(const ExtendParams, const int);
+
+template <bool kBf16>
+KernelFn pick_kernel(int emu, bool prof) {
+  if (prof) return tc64::extend_tc64_kernel<kBf16, 0, true>;
+  return emu == 1 ? tc64::extend_tc64_kernel<kBf16, 1, false> : tc64::extend_tc64_kernel<kBf16, 0, false>;
+}
+}  // namespace
+
+int extend_tc64_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
+  KernelFn kern;
+  if (p.window >= 0) {
+    if (kvb == 1)
+      kern = q_bf16 ? tc64::extend_tc64_kernel<false, 0, false, true, true, true>
+                    : tc64::extend_tc64_kernel<false, 0, false, true, false, true>;
+    else
+      kern = q_bf16 ? tc64::extend_tc64_kernel<true, 0, false, false, false, true>
+                    : tc64::extend_tc64_kernel<false, 0, false, false, false, true>;
+  } else if (kvb == 1)  // FP8-E4M3 pool: f16 MMA, e4m3 expanded by the producers; bf16 q converted on load
+    kern = q_bf16 ? tc64::extend_tc64_kernel<false, 0, false, true, true> : tc64::extend_tc64_kernel<false, 0, false, true, false>;
+  else
+    kern = q_bf16 ? pick_kernel<true>(p.exp_emu, p.prof != nullptr) : pick_kernel<false>(p.exp_emu, p.prof != nullptr);
+  // opt in to the large dynamic shared memory once per kernel instance (cheap host call, no device sync)
+  B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc64::kSmemBytes));
+  const int pair_heads = (p.G % 2 == 0) ? 1 : 0;
+  const int q_tiles = (p.max_extend_len + tc64::kTile - 1) / tc64::kTile;
+  const int nz = pair_heads ? q_tiles : (q_tiles + 1) / 2;
+  dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.grid_order ? nz : p.bs, p.grid_order ? p.bs : nz);
+  B2_REQUIRE(grid.y <= 65535 && grid.z <= 65535, B200ATTN_ERR_UNSUPPORTED, "extend: batch %d or %d q tiles exceed the grid",
+             p.bs, q_tiles);
+  kern<<<grid, tc64::kThreads, tc64::kSmemBytes, st>>>(p, pair_heads);
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
+}
+
+}  // namespace b200attn
