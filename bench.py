@@ -37,7 +37,7 @@ sys.path.insert(0, str(ROOT))
 import torch  # noqa: E402
 
 LAYERS = 32  # Llama-3-8B
-NCU_DECODE_C2_TRAFFIC_BYTES = 4_302_502_000 + 8_256_512  # ncu --set full, see profiles/README.md
+NCU_DECODE_C2_TRAFFIC_BYTES = 4_302_531_000 + 7_630_336  # ncu --set full (profiles/r01b_ncu_decode_c2.txt), see profiles/README.md
 READ_STREAM_CEILING_GBS = 7272.3  # coalesced read-only stream, scripts/ubench/hbm_read.cu (profiles/r01_ubench_hbm_read.txt)
 
 
@@ -227,8 +227,8 @@ def _run_decode(args, rank, world, dev, peaks):
                      "read_stream_ceiling_gbs": READ_STREAM_CEILING_GBS,
                      "us_per_launch": round(ms_kernel * 1e3, 2), "bytes_per_launch": kv_bytes_layer,
                      # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this shape, one launch, from the
-                     # committed `ncu --set full` capture profiles/r01_ncu_decode_c2.txt (4.302502 GB + 8.257 MB)
-                     "traffic": NCU_DECODE_C2_TRAFFIC_BYTES, "traffic_source": "profiles/r01_ncu_decode_c2.txt"},
+                     # committed `ncu --set full` capture profiles/r01b_ncu_decode_c2.txt (4.302531 GB + 7.630 MB)
+                     "traffic": NCU_DECODE_C2_TRAFFIC_BYTES, "traffic_source": "profiles/r01b_ncu_decode_c2.txt"},
         "clocks": clocks,
     }
     return line, (case, r)

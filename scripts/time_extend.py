@@ -37,7 +37,10 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
-    print(f"extend bs={bs} P={P} E={E} fp8={fp8} page={page}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
+    # bit-level checksum of the output: lets two runs with different dev knobs (B200ATTN_EXP_EMU=4 = legacy two-pass
+    # softmax schedule, B200ATTN_EXTEND_TC=64) be compared for bit-identity
+    chk = int(out.view(torch.int16).to(torch.int64).sum().item())
+    print(f"extend bs={bs} P={P} E={E} fp8={fp8} page={page}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s  checksum {chk}", flush=True)
     if prof is not None:
         pr = prof.cpu().view(16, 8)
         n_it = (P + E + 127) // 128
