@@ -93,7 +93,7 @@ struct Prof<false> {
 //   kWin : sliding-window variant -- keys [0, nlo) of the tile are invisible too, and a row may see nothing at all
 //          in its first tiles: the running maximum then stays -inf until the first visible key (no rescale needed,
 //          l and O are still exact zeros)
-template <bool kBf16, bool kMask, int kEmuIn, bool kProf, bool kWin = false>
+template <bool kBf16, bool kMask, int kEmu, bool kProf, bool kWin = false>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const uint32_t bar_s,
                                              const uint32_t bar_p, const int j, const int nvis,
                                              const float scale_log2, float& m_used, float& l, Prof<kProf>& prof,
@@ -106,102 +106,6 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   for (int c = 0; c < 4; ++c) ptx::tmem_ld32(tS + c * 32, s + 32 * c);
   ptx::tmem_wait_ld();
   prof.mark(1);
-
-  // kEmuIn == 4 selects the legacy two-pass schedule (row max first, then the exponentials) on every tile
-  constexpr bool kFused = kEmuIn != 4;
-  constexpr int kEmu = kEmuIn == 4 ? 0 : kEmuIn;
-  if constexpr (!kMask && kFused) {
-    if (j > 0) {
-      // Fused schedule for the common tile (fully visible, not the first): the exponentials of the first 64 keys
-      // are computed OPTIMISTICALLY against the current reference maximum while the FMNMX chain of the whole row
-      // runs underneath them (the loop is MUFU-bound, the ALU work is free) -- the separate 128-element max pass of
-      // the two-pass schedule disappears from the softmax -> PV -> QK chain.  The decision "does the maximum grow
-      // by more than the threshold" is taken before this thread group hands the first half over, i.e. while O_t is
-      // still stable (PV(j-1) complete, PV(j) not started), so the rescale stays legal; the first half is then
-      // recomputed (rare: a row's maximum settles within its first tiles).  Results are bit-identical to the
-      // two-pass schedule: same reference maximum, same operations per element.
-      const float2 sc2 = make_float2(scale_log2, scale_log2);
-      float2 nm2 = make_float2(-m_used, -m_used);
-      float2 sum2[4];
-      uint32_t pk[32];
-      float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, mxb[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-      // s[0..63] are consumed here (the slow path reloads them from tensor memory, where S is still intact: P has
-      // not been stored yet), so only the second half of the row and the packed P stay live
-      auto first_half = [&](const bool track) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) sum2[q] = make_float2(0.f, 0.f);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int e = 2 * i;
-          if (track) {
-            mxa[i & 3] = fmaxf(fmaxf(mxa[i & 3], __uint_as_float(s[e])), __uint_as_float(s[e + 1]));
-            mxb[i & 3] = fmaxf(fmaxf(mxb[i & 3], __uint_as_float(s[64 + e])), __uint_as_float(s[64 + e + 1]));
-          }
-          float2 x = ptx::ffma2(make_float2(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), sc2, nm2);
-          if ((i & 3) < kEmu) {
-            x = ptx::exp2_poly2(x);
-          } else {
-            x.x = fast_exp2(x.x);
-            x.y = fast_exp2(x.y);
-          }
-          sum2[i & 3] = ptx::fadd2(sum2[i & 3], x);
-          pk[i] = pack2<kBf16>(x.x, x.y);
-        }
-      };
-      first_half(true);
-      const float mx = fmaxf(fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3])),
-                             fmaxf(fmaxf(mxb[0], mxb[1]), fmaxf(mxb[2], mxb[3]))) * scale_log2;
-      prof.mark(2);
-      const bool grow = mx > m_used + kRescaleThreshold;
-      if (__any_sync(0xffffffffu, grow)) {
-        const float m_new = grow ? mx : m_used;
-        const float f = (kWin && !grow) ? 1.f : fast_exp2(m_used - m_new);  // kWin: m_used may still be -inf
-        l *= f;
-        m_used = m_new;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t o[32];
-          ptx::tmem_ld32(tO + c * 32, o);
-          ptx::tmem_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-          ptx::tmem_st32(tO + c * 32, o);
-        }
-        ptx::tmem_wait_st();
-        nm2 = make_float2(-m_used, -m_used);
-        ptx::tmem_ld32(tS, s);
-        ptx::tmem_ld32(tS + 32, s + 32);
-        ptx::tmem_wait_ld();
-        first_half(false);  // against the new reference
-      }
-      prof.mark(3);
-      ptx::tmem_st32(tS, pk);
-      ptx::tmem_wait_st();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_p);
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int e = 64 + 2 * i;
-        float2 x = ptx::ffma2(make_float2(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), sc2, nm2);
-        if ((i & 3) < kEmu) {
-          x = ptx::exp2_poly2(x);
-        } else {
-          x.x = fast_exp2(x.x);
-          x.y = fast_exp2(x.y);
-        }
-        sum2[i & 3] = ptx::fadd2(sum2[i & 3], x);
-        pk[i] = pack2<kBf16>(x.x, x.y);
-      }
-      ptx::tmem_st32(tS + 32, pk);
-      ptx::tmem_wait_st();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_p + 8u);
-      const float2 st = ptx::fadd2(ptx::fadd2(sum2[0], sum2[1]), ptx::fadd2(sum2[2], sum2[3]));
-      l += st.x + st.y;
-      prof.mark(4);
-      return;
-    }
-  }
 
   if constexpr (kMask) {
 #pragma unroll
@@ -726,14 +630,14 @@ KernelFn pick_kernel(int emu, bool prof) {
   switch (emu) {
     case 0: return tc::extend_tc_kernel<kBf16, 0, false>;
     case 1: return tc::extend_tc_kernel<kBf16, 1, false>;
-    case 4: return tc::extend_tc_kernel<kBf16, 4, false>;  // legacy two-pass softmax schedule (A/B)
+    case 3: return tc::extend_tc_kernel<kBf16, 3, false>;
     default: return tc::extend_tc_kernel<kBf16, 2, false>;
   }
 }
 }  // namespace
 
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
-  const int emu = (p.exp_emu >= 0 && p.exp_emu <= 4) ? p.exp_emu : 2;
+  const int emu = (p.exp_emu >= 0 && p.exp_emu <= 3) ? p.exp_emu : 2;
   KernelFn kern;
   if (p.window >= 0) {
     if (kvb == 1)
