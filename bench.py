@@ -34,6 +34,13 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+# stdout carries exactly one JSON line.  Native libraries write to file descriptor 1 behind Python's back (NCCL prints
+# "NCCL version ..." there on boxes that export NCCL_DEBUG), so fd 1 is pointed at stderr for the whole run and the
+# JSON line goes to a private duplicate of the original stdout.
+sys.stdout.flush()
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
 import torch  # noqa: E402
 
 LAYERS = 32  # Llama-3-8B
@@ -373,7 +380,7 @@ def main() -> None:
     if args.impl == "reference":
         line = _run_reference(args, rank, world)
         if line is not None:
-            print(json.dumps(line), flush=True)
+            print(json.dumps(line), file=_JSON_OUT, flush=True)
         return
 
     if not torch.cuda.is_available():
@@ -390,7 +397,7 @@ def main() -> None:
     if rank == 0:
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = _cpu_baseline()
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     tp.barrier(world)
     if world > 1:
         torch.distributed.destroy_process_group()
