@@ -68,6 +68,12 @@ def main():
         run("bs16 ctx1024 32/8 bf16", 16, 32, 8, 128, [1024] * 16, False, (148,))
         run("bs1 ctx32768 32/8 bf16", 1, 32, 8, 128, [32768], False, (148,))
         run("bs64 ctx512 32/8 bf16", 64, 32, 8, 128, [512] * 64, False, (148,))
+    if which in ("lowbatch",):
+        # the low-batch regime: few requests, long contexts -- split-KV has to spread ONE request over all SMs
+        for bs, ctx in ((1, 4096), (1, 32768), (1, 131072), (4, 32768), (8, 8192), (16, 4096), (32, 4096), (64, 4096)):
+            run(f"bf16 32/8 bs{bs} ctx{ctx}", bs, 32, 8, 128, [ctx] * bs, False, (148, 296))
+        for bs, ctx in ((1, 32768), (8, 8192), (32, 8192)):
+            run(f"fp8 8/1 bs{bs} ctx{ctx}", bs, 8, 1, 128, [ctx] * bs, True, (148, 296))
 
 
 if __name__ == "__main__":

@@ -563,11 +563,16 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
 // LSE merge of the pieces of every request that was cut across CTAs
 // (reference: triton_ops/decode_attention.py:492-552, sgl-kernel/csrc/cpu/decode.cpp:812-860).
 // One warp per (request, q head).
+constexpr int kMergeWarps = 8;
+
+// One CTA (8 warps) per (request, q head): the warps split the partials of a request between them -- at low batch a
+// single request is cut across all persistent CTAs (up to n_ctas partials), and walking them with one warp made this
+// kernel longer than stage 1 (72 us at bs 1 against 9 us; profiles/README.md) -- and combine through shared memory.
+// Requests that one CTA finished (the common case at large batch) leave after two loads.
 template <int D, bool kBf16>
-__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= p.bs * p.Hq) return;
-  const int i = warp / p.Hq, head = warp % p.Hq;
+__global__ void __launch_bounds__(kMergeWarps * 32) decode_merge_kernel(const DecodeParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x / p.Hq, head = blockIdx.x % p.Hq;
   const int32_t* plan = p.plan;
   const int W = plan[kPlanUnitsPerCta];
   const int32_t* cum = plan + kPlanHeader;
@@ -579,24 +584,35 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
   float* lse_dst = p.lse_out ? p.lse_out + static_cast<int64_t>(i) * p.lse_req_stride + sub * p.Hq_real + head_real : nullptr;
   constexpr int EPL = D / 32;  // elements per lane
   if (c1 == c0) {  // empty request: defined as zeros
+    if (warp == 0) {
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
-    if (lse_dst != nullptr && lane == 0) *lse_dst = -INFINITY;
+      for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
+      if (lse_dst != nullptr && lane == 0) *lse_dst = -INFINITY;
+    }
     return;
   }
   const int cta0 = c0 / W, cta1 = (c1 - 1) / W;
   const int n = cta1 - cta0 + 1;
   if (n == 1) return;  // written directly by the decode kernel
+  __shared__ float s_red[kMergeWarps];
+  __shared__ float s_acc[kMergeWarps][D];
   auto slot_of = [&](int k) { return k == 0 ? 2 * cta0 + 1 : 2 * (cta0 + k); };
   float mx = -INFINITY;
-  for (int k = lane; k < n; k += 32) mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
+  for (int k = threadIdx.x; k < n; k += kMergeWarps * 32)
+    mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
 #pragma unroll
   for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+  if (lane == 0) s_red[warp] = mx;
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < kMergeWarps; ++w) mx = fmaxf(mx, s_red[w]);
+  __syncthreads();  // s_red is reused for the weight sums
   float acc[EPL];
 #pragma unroll
   for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
   float wsum = 0.f;
-  for (int k = 0; k < n; ++k) {
+#pragma unroll 4
+  for (int k = warp; k < n; k += kMergeWarps) {
     const int64_t slot = slot_of(k);
     const float lse = p.ws_lse[slot * p.Hq + head];
     const float w = (lse == -INFINITY) ? 0.f : __expf(lse - mx);
@@ -610,6 +626,20 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
     }
     wsum += w;
   }
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) s_acc[warp][lane * EPL + e] = acc[e];
+  if (lane == 0) s_red[warp] = wsum;
+  __syncthreads();
+  if (warp != 0) return;
+  wsum = 0.f;
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+#pragma unroll
+  for (int w = 0; w < kMergeWarps; ++w) {
+    wsum += s_red[w];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) acc[e] += s_acc[w][lane * EPL + e];
+  }
   const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
 #pragma unroll
   for (int e = 0; e < EPL; e += 2)
@@ -617,7 +647,6 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
   if (lse_dst != nullptr && lane == 0) *lse_dst = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
 }
 
-// ---------------------------------------------------------------------------------------
 template <int D, int HB, int KVB, bool kQBf16, bool kG8>
 static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
   constexpr int kWant = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
@@ -717,14 +746,14 @@ static int launch_partial(const DecodeParams& p, int D, int kvb, bool q_bf16, cu
 }
 
 static int launch_merge(const DecodeParams& p, int D, bool q_bf16, cudaStream_t st) {
-  const int warps = p.bs * p.Hq;
-  const int blocks = (warps * 32 + 127) / 128;
+  const int blocks = p.bs * p.Hq;  // one CTA per (request, q head)
+  constexpr int kT = kMergeWarps * 32;
   if (D == 128) {
-    if (q_bf16) decode_merge_kernel<128, true><<<blocks, 128, 0, st>>>(p);
-    else decode_merge_kernel<128, false><<<blocks, 128, 0, st>>>(p);
+    if (q_bf16) decode_merge_kernel<128, true><<<blocks, kT, 0, st>>>(p);
+    else decode_merge_kernel<128, false><<<blocks, kT, 0, st>>>(p);
   } else {
-    if (q_bf16) decode_merge_kernel<64, true><<<blocks, 128, 0, st>>>(p);
-    else decode_merge_kernel<64, false><<<blocks, 128, 0, st>>>(p);
+    if (q_bf16) decode_merge_kernel<64, true><<<blocks, kT, 0, st>>>(p);
+    else decode_merge_kernel<64, false><<<blocks, kT, 0, st>>>(p);
   }
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
