@@ -39,7 +39,20 @@ def run(name, bs, Hq, Hkv, D, lens, fp8, n_ctas_list=(148,), page_size=1, table=
                                 case.seq_lens, plan, n_ctas, ws, case.sm_scale,
                                 kv_dtype=torch.float8_e4m3fn if fp8 else None)
         ms = time_ms(fn)
-        res.append(dict(name=name, n_ctas=n_ctas, us=round(ms * 1e3, 1), gbs=round(nbytes / ms / 1e6, 1)))
+        # the same call replayed from a CUDA graph of 10 (device time without the host's launch path)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for _ in range(10):
+                fn()
+        ms_g = time_ms(g.replay, reps=5, warm=2) / 10
+        del g
+        res.append(dict(name=name, n_ctas=n_ctas, us=round(ms * 1e3, 1), gbs=round(nbytes / ms / 1e6, 1),
+                        graph_us=round(ms_g * 1e3, 1), graph_gbs=round(nbytes / ms_g / 1e6, 1)))
         print(json.dumps(res[-1]), flush=True)
     del case
     torch.cuda.empty_cache()
