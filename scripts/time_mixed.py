@@ -47,6 +47,25 @@ def main():
         fb = r.batch(r.itf.ForwardMode.MIXED)
         r.backend.init_forward_metadata(fb)
         res[route] = t_ms(lambda: r.layer.forward(q, k, v, fb))
+    r.backend.route_decode_tail = True
+    r.backend.overlap_mixed = True
+    fb = r.batch(r.itf.ForwardMode.MIXED)
+    r.backend.init_forward_metadata(fb)
+    ref_out = None
+    r.backend.overlap_mixed = False
+    ref_out = r.layer.forward(q, k, v, fb).clone()
+    r.backend.overlap_mixed = True
+    ov_out = r.layer.forward(q, k, v, fb)
+    torch.cuda.synchronize()
+    same = torch.equal(ref_out, ov_out)
+    res["overlap"] = t_ms(lambda: r.layer.forward(q, k, v, fb))
+    print(f"  decode tail on a side stream : {res['overlap']:8.3f} ms per layer   (bit-identical to the serial route: {same})")
+    r.backend.overlap_mixed = 2
+    ov2 = r.layer.forward(q, k, v, fb)
+    torch.cuda.synchronize()
+    same2 = torch.equal(ref_out, ov2)
+    res["overlap2"] = t_ms(lambda: r.layer.forward(q, k, v, fb))
+    print(f"  same, prefill launched first : {res['overlap2']:8.3f} ms per layer   (bit-identical: {same2})")
     print(f"C5 per-rank mixed forward: sum L = {sum(lens)} tokens, decode rows {n_dec}, prefill rows {n_ext} x {E}")
     print(f"  decode tail -> decode kernel : {res[True]:8.3f} ms per layer")
     print(f"  all rows -> extend kernels   : {res[False]:8.3f} ms per layer")

@@ -169,6 +169,11 @@ def test_c5_shaped_mixed_forward_scaled_down(device):
     assert H.pools_equal(dk, kp) and H.pools_equal(dv, vp), "FP8 KV write of the mixed forward"
     assert r.backend.forward_metadata.n_decode_tail == n_dec
     H.assert_close(got, H.oracle_extend(case, kp, vp), what="C5-shaped mixed forward")
+    # the two-stream routes (decode tail on a side stream, either launch order) are bit-identical to the serial one
+    for mode in (True, 2):
+        r.backend.overlap_mixed = mode
+        again = r.forward(r.itf.ForwardMode.MIXED)
+        assert torch.equal(again, got), f"overlap_mixed={mode}"
 
 
 def test_extend_chunked_prefill_equals_one_shot(device):
