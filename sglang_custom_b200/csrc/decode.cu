@@ -48,6 +48,7 @@ struct DecodeParams {
   // multi-query rows (b200attn_decode_multiq): the G = nq * Gr MMA rows of a kv head are nq query tokens x Gr q heads
   // that share the request's keys.  Row r -> token r / Gr, q head kv_head * Gr + r % Gr.  Plain decode: nq = 1, Gr = G.
   int Gr, Hq_real;
+  int merge_hpc;  // q heads served by one CTA of the merge kernel (set by launch_merge)
   int64_t q_sub_stride, out_sub_stride;  // stride between the nq tokens of a request (elements)
   int64_t lse_req_stride;                // lse_out: [request][token][Hq_real]
   int n_ctas;
@@ -564,87 +565,135 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
 // (reference: triton_ops/decode_attention.py:492-552, sgl-kernel/csrc/cpu/decode.cpp:812-860).
 // One warp per (request, q head).
 constexpr int kMergeWarps = 8;
+constexpr int kMergeCoopMin = 8;  // up to this many partials a single warp merges a head on its own
 
-// One CTA (8 warps) per (request, q head): the warps split the partials of a request between them -- at low batch a
-// single request is cut across all persistent CTAs (up to n_ctas partials), and walking them with one warp made this
-// kernel longer than stage 1 (72 us at bs 1 against 9 us; profiles/README.md) -- and combine through shared memory.
-// Requests that one CTA finished (the common case at large batch) leave after two loads.
+// One CTA (8 warps) per (request, group of p.merge_hpc q heads): the warps split the partials of a request between
+// them -- at low batch a single request is cut across all persistent CTAs (up to n_ctas partials), and walking them
+// with one warp made this kernel longer than stage 1 (72 us at bs 1 against 9 us; profiles/README.md) -- and combine
+// through shared memory, one head after the other.  merge_hpc is chosen on the host so that large batches launch
+// about a thousand CTAs (one CTA per (request, head) cost 10 us of pure CTA turnover at bs 256 x 32 heads): requests
+// that one stage-1 CTA finished -- the common case there -- leave after two loads for the whole head group.
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kMergeWarps * 32) decode_merge_kernel(const DecodeParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int i = blockIdx.x / p.Hq, head = blockIdx.x % p.Hq;
+  const int groups = p.Hq / p.merge_hpc;
+  const int i = blockIdx.x / groups, head0 = (blockIdx.x % groups) * p.merge_hpc;
   const int32_t* plan = p.plan;
   const int W = plan[kPlanUnitsPerCta];
   const int32_t* cum = plan + kPlanHeader;
   const int c0 = cum[i], c1 = cum[i + 1];
-  const int kvh = head / p.G, r = head % p.G;  // virtual head -> (token, real q head), see DecodeParams
-  const int sub = r / p.Gr, head_real = kvh * p.Gr + r % p.Gr;
-  uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + sub * p.out_sub_stride +
-                  static_cast<int64_t>(head_real) * D;
-  float* lse_dst = p.lse_out ? p.lse_out + static_cast<int64_t>(i) * p.lse_req_stride + sub * p.Hq_real + head_real : nullptr;
   constexpr int EPL = D / 32;  // elements per lane
-  if (c1 == c0) {  // empty request: defined as zeros
-    if (warp == 0) {
-#pragma unroll
-      for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
-      if (lse_dst != nullptr && lane == 0) *lse_dst = -INFINITY;
-    }
-    return;
-  }
-  const int cta0 = c0 / W, cta1 = (c1 - 1) / W;
+  const bool empty = c1 == c0;
+  const int cta0 = c0 / W, cta1 = empty ? cta0 : (c1 - 1) / W;
   const int n = cta1 - cta0 + 1;
-  if (n == 1) return;  // written directly by the decode kernel
+  if (!empty && n == 1) return;  // written directly by the decode kernel
   __shared__ float s_red[kMergeWarps];
   __shared__ float s_acc[kMergeWarps][D];
   auto slot_of = [&](int k) { return k == 0 ? 2 * cta0 + 1 : 2 * (cta0 + k); };
-  float mx = -INFINITY;
-  for (int k = threadIdx.x; k < n; k += kMergeWarps * 32)
-    mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
+  if (empty || n <= kMergeCoopMin) {
+    // few partials (the usual 2 of a request that straddles one share boundary) or none: one warp per head, no
+    // shared memory, no CTA barrier -- the heads of the group proceed in parallel
+    for (int head = head0 + warp; head < head0 + p.merge_hpc; head += kMergeWarps) {
+      const int kvh = head / p.G, r = head % p.G;
+      const int sub = r / p.Gr, head_real = kvh * p.Gr + r % p.Gr;
+      uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + sub * p.out_sub_stride +
+                      static_cast<int64_t>(head_real) * D;
+      float* lse_dst = p.lse_out ? p.lse_out + static_cast<int64_t>(i) * p.lse_req_stride + sub * p.Hq_real + head_real : nullptr;
+      if (empty) {  // empty request: defined as zeros
 #pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
-  if (lane == 0) s_red[warp] = mx;
-  __syncthreads();
+        for (int e = 0; e < EPL; ++e) dst[lane * EPL + e] = 0;
+        if (lse_dst != nullptr && lane == 0) *lse_dst = -INFINITY;
+        continue;
+      }
+      float mx = -INFINITY;
+      for (int k = lane; k < n; k += 32) mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
 #pragma unroll
-  for (int w = 0; w < kMergeWarps; ++w) mx = fmaxf(mx, s_red[w]);
-  __syncthreads();  // s_red is reused for the weight sums
-  float acc[EPL];
+      for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+      float acc[EPL];
 #pragma unroll
-  for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
-  float wsum = 0.f;
+      for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+      float wsum = 0.f;
 #pragma unroll 4
-  for (int k = warp; k < n; k += kMergeWarps) {
-    const int64_t slot = slot_of(k);
-    const float lse = p.ws_lse[slot * p.Hq + head];
-    const float w = (lse == -INFINITY) ? 0.f : __expf(lse - mx);
-    const float* src = p.ws_o + (slot * p.Hq + head) * D + lane * EPL;
-    if constexpr (EPL == 4) {
-      const float4 x = *reinterpret_cast<const float4*>(src);
-      acc[0] += w * x.x; acc[1] += w * x.y; acc[2] += w * x.z; acc[3] += w * x.w;
-    } else {
-      const float2 x = *reinterpret_cast<const float2*>(src);
-      acc[0] += w * x.x; acc[1] += w * x.y;
+      for (int k = 0; k < n; ++k) {
+        const int64_t slot = slot_of(k);
+        const float lse = p.ws_lse[slot * p.Hq + head];
+        const float w = (lse == -INFINITY) ? 0.f : __expf(lse - mx);
+        const float* src = p.ws_o + (slot * p.Hq + head) * D + lane * EPL;
+        if constexpr (EPL == 4) {
+          const float4 x = *reinterpret_cast<const float4*>(src);
+          acc[0] += w * x.x; acc[1] += w * x.y; acc[2] += w * x.z; acc[3] += w * x.w;
+        } else {
+          const float2 x = *reinterpret_cast<const float2*>(src);
+          acc[0] += w * x.x; acc[1] += w * x.y;
+        }
+        wsum += w;
+      }
+      const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+#pragma unroll
+      for (int e = 0; e < EPL; e += 2)
+        *reinterpret_cast<uint32_t*>(dst + lane * EPL + e) = pack2<kBf16>(acc[e] * inv, acc[e + 1] * inv);
+      if (lse_dst != nullptr && lane == 0) *lse_dst = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
     }
-    wsum += w;
+    return;
   }
+  // many partials: the eight warps split them, one head after the other
+  for (int head = head0; head < head0 + p.merge_hpc; ++head) {
+    const int kvh = head / p.G, r = head % p.G;  // virtual head -> (token, real q head), see DecodeParams
+    const int sub = r / p.Gr, head_real = kvh * p.Gr + r % p.Gr;
+    uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + i * p.out_tok_stride + sub * p.out_sub_stride +
+                    static_cast<int64_t>(head_real) * D;
+    float* lse_dst = p.lse_out ? p.lse_out + static_cast<int64_t>(i) * p.lse_req_stride + sub * p.Hq_real + head_real : nullptr;
+    float mx = -INFINITY;
+    for (int k = threadIdx.x; k < n; k += kMergeWarps * 32)
+      mx = fmaxf(mx, p.ws_lse[static_cast<int64_t>(slot_of(k)) * p.Hq + head]);
 #pragma unroll
-  for (int e = 0; e < EPL; ++e) s_acc[warp][lane * EPL + e] = acc[e];
-  if (lane == 0) s_red[warp] = wsum;
-  __syncthreads();
-  if (warp != 0) return;
-  wsum = 0.f;
+    for (int s = 16; s >= 1; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
 #pragma unroll
-  for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+    for (int w = 0; w < kMergeWarps; ++w) mx = fmaxf(mx, s_red[w]);
+    __syncthreads();  // s_red is reused for the weight sums
+    float acc[EPL];
 #pragma unroll
-  for (int w = 0; w < kMergeWarps; ++w) {
-    wsum += s_red[w];
+    for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+    float wsum = 0.f;
+#pragma unroll 4
+    for (int k = warp; k < n; k += kMergeWarps) {
+      const int64_t slot = slot_of(k);
+      const float lse = p.ws_lse[slot * p.Hq + head];
+      const float w = (lse == -INFINITY) ? 0.f : __expf(lse - mx);
+      const float* src = p.ws_o + (slot * p.Hq + head) * D + lane * EPL;
+      if constexpr (EPL == 4) {
+        const float4 x = *reinterpret_cast<const float4*>(src);
+        acc[0] += w * x.x; acc[1] += w * x.y; acc[2] += w * x.z; acc[3] += w * x.w;
+      } else {
+        const float2 x = *reinterpret_cast<const float2*>(src);
+        acc[0] += w * x.x; acc[1] += w * x.y;
+      }
+      wsum += w;
+    }
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) acc[e] += s_acc[w][lane * EPL + e];
+    for (int e = 0; e < EPL; ++e) s_acc[warp][lane * EPL + e] = acc[e];
+    if (lane == 0) s_red[warp] = wsum;
+    __syncthreads();
+    if (warp == 0) {
+      wsum = 0.f;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+#pragma unroll
+      for (int w = 0; w < kMergeWarps; ++w) {
+        wsum += s_red[w];
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) acc[e] += s_acc[w][lane * EPL + e];
+      }
+      const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+#pragma unroll
+      for (int e = 0; e < EPL; e += 2)
+        *reinterpret_cast<uint32_t*>(dst + lane * EPL + e) = pack2<kBf16>(acc[e] * inv, acc[e + 1] * inv);
+      if (lse_dst != nullptr && lane == 0) *lse_dst = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
+    }
+    __syncthreads();  // s_red / s_acc are rewritten for the next head
   }
-  const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
-#pragma unroll
-  for (int e = 0; e < EPL; e += 2)
-    *reinterpret_cast<uint32_t*>(dst + lane * EPL + e) = pack2<kBf16>(acc[e] * inv, acc[e + 1] * inv);
-  if (lse_dst != nullptr && lane == 0) *lse_dst = wsum > 0.f ? mx + __logf(wsum) : -INFINITY;
 }
 
 template <int D, int HB, int KVB, bool kQBf16, bool kG8>
@@ -731,6 +780,7 @@ static int decode_setup(DecodeParams& p, const void* q, int64_t q_tok_stride, vo
   p.pool_tok_stride = pool_tok_stride; p.table_stride = table_stride;
   p.idx_is_i64 = idx_is_i64;
   p.bs = bs; p.Hq = Hq; p.Hkv = Hkv; p.G = G;
+  p.merge_hpc = 1;
   p.Gr = G; p.Hq_real = Hq; p.q_sub_stride = 0; p.out_sub_stride = 0; p.lse_req_stride = Hq;
   p.n_ctas = n_ctas;
   p.scale_raw = sm_scale * k_scale;
@@ -746,14 +796,19 @@ static int launch_partial(const DecodeParams& p, int D, int kvb, bool q_bf16, cu
 }
 
 static int launch_merge(const DecodeParams& p, int D, bool q_bf16, cudaStream_t st) {
-  const int blocks = p.bs * p.Hq;  // one CTA per (request, q head)
+  // heads per CTA: the largest power of two dividing Hq that keeps about a thousand CTAs in the grid
+  int hpc = 1;
+  while (hpc * 2 <= p.Hq && p.Hq % (hpc * 2) == 0 && static_cast<int64_t>(p.bs) * p.Hq / (hpc * 2) >= 1024) hpc *= 2;
+  DecodeParams pm = p;
+  pm.merge_hpc = hpc;
+  const int blocks = p.bs * (p.Hq / hpc);
   constexpr int kT = kMergeWarps * 32;
   if (D == 128) {
-    if (q_bf16) decode_merge_kernel<128, true><<<blocks, kT, 0, st>>>(p);
-    else decode_merge_kernel<128, false><<<blocks, kT, 0, st>>>(p);
+    if (q_bf16) decode_merge_kernel<128, true><<<blocks, kT, 0, st>>>(pm);
+    else decode_merge_kernel<128, false><<<blocks, kT, 0, st>>>(pm);
   } else {
-    if (q_bf16) decode_merge_kernel<64, true><<<blocks, kT, 0, st>>>(p);
-    else decode_merge_kernel<64, false><<<blocks, kT, 0, st>>>(p);
+    if (q_bf16) decode_merge_kernel<64, true><<<blocks, kT, 0, st>>>(pm);
+    else decode_merge_kernel<64, false><<<blocks, kT, 0, st>>>(pm);
   }
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
