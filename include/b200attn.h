@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_VERSION 101 /* 0.1.1 */
+#define B200ATTN_VERSION 102 /* 0.1.2: + decode_plan_window, decode_multiq, extend_masked, EXTEND_TCGEN05_STEP64 */
 
 /* element types */
 #define B200ATTN_BF16 0
