@@ -444,3 +444,29 @@ def test_decode_multiq_vs_oracle(bs, Hq, Hkv, D, lens, nq, kw, device):
     H.assert_close(outs[0][0], outs[1][0], 4e-3, 4e-4, what="split invariance")
     fin = torch.isfinite(outs[0][1])
     assert float((outs[0][1][fin] - outs[1][1][fin]).abs().max()) < 1e-3
+
+
+def test_target_verify_full_size_routes_agree(device):
+    """Verify batch at the size the timing script reports (bs 256, ctx 4096, 8 draft tokens, 32/8 heads, P = 1M rows):
+    the decode_multiq + masked draft part + LSE merge route against the single masked extend kernel (both checked
+    against the oracle at small sizes above), and against the plain causal extend when the mask is the causal one."""
+    from sglang_custom_b200 import harness
+    bs, L, Hq, Hkv, D, nd = 256, 4096, 32, 8, 128, 8
+    c = synth.make_case_device(bs, Hq, Hkv, D, [L + nd] * bs, device, extend_lens=[nd] * bs, seed=1238)
+    g = torch.Generator().manual_seed(3)
+    blk = tm.tree_mask(L, nd, g)
+    mask = blk.reshape(-1).repeat(bs)
+    r = harness.Runner(c, device, num_draft_tokens=nd)
+    outs = {}
+    for via in (True, False):
+        r.backend.verify_via_decode = via
+        outs[via] = r.forward(fb=r.verify_batch(mask), save_kv_cache=False).clone()
+    H.assert_close(outs[True], outs[False], 8e-3, 6e-4, what="verify routes at full size")
+    causal = torch.cat([torch.ones(nd, L, dtype=torch.bool), torch.tril(torch.ones(nd, nd)).bool()], 1).reshape(-1).repeat(bs)
+    r.backend.verify_via_decode = True
+    got = r.forward(fb=r.verify_batch(causal), save_kv_cache=False)
+    plain = torch.empty_like(c.q)
+    ops.extend(c.q, plain, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.seq_lens, c.extend_seq_lens,
+               c.extend_prefix_lens, c.extend_start_loc, nd, c.sm_scale, impl=_lib.EXTEND_MMA)
+    torch.cuda.synchronize(device)
+    H.assert_close(got, plain, 8e-3, 6e-4, what="causal tree mask == plain causal extend")
