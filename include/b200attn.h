@@ -23,6 +23,7 @@
  *   b200attn_decode_multiq       cached-prefix part of TARGET_VERIFY batches (triton_backend.py:227-264)
  *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
  *   b200attn_extend_masked       triton_ops/extend_attention.py:158-175,236-247 (sliding window, custom mask)
+ *   b200attn_check_loc           mem_cache/memory_pool.py:457-458 (`buf[loc] = x`: which duplicates are legal)
  *   b200attn_flatten_kv_indices  layers/attention/utils.py:5-41 (create_flashinfer_kv_indices_triton)
  *   b200attn_gather_kv           torch_native_backend.py:92-94,155-157 (k_cache[per_req_tokens] page gather)
  *
@@ -48,7 +49,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_VERSION 102 /* 0.1.2: + decode_plan_window, decode_multiq, extend_masked, EXTEND_TCGEN05_STEP64 */
+#define B200ATTN_VERSION 200 /* 0.2.0: + check_loc; EXTEND_TCGEN05_STEP64 removed */
 
 /* element types */
 #define B200ATTN_BF16 0
@@ -90,9 +91,11 @@ int b200attn_device_info(int* sm_count, int* cc_major, int* cc_minor, int* max_s
  *   host scalar *_scale_host is used; a host scalar of 0 means "no scaling" (None).
  *   writeback_scaled != 0 reproduces the reference's in-place `cache_k.div_(scale)`
  *   side effect on the caller's k/v tensors (memory_pool.py:437-440).
- * Duplicate `loc` entries (padded CUDA-graph rows all map to slot 0) are
- * last-writer-wins in the reference; here the order is unspecified, which only
- * matters for the dummy slot. */
+ * Duplicate `loc` entries: the reference is last-writer-wins on the CPU (`buf[loc] = x`,
+ * memory_pool.py:457-458) and unspecified on CUDA (index_put_ without accumulate); here the
+ * order is unspecified too.  SGLang only ever produces duplicates inside the dummy page
+ * [0, page_size) (padded CUDA-graph rows, cuda_graph_runner.py:686-695), whose content is
+ * never read unmasked; b200attn_check_loc below detects any other duplicate. */
 int b200attn_kv_write(const void* k, const void* v, int64_t k_tok_stride, int64_t k_head_stride,
                       int64_t v_tok_stride, int64_t v_head_stride, const int64_t* loc, int T, int Hkv,
                       int D, void* k_pool, void* v_pool, int64_t pool_tok_stride, int in_dtype,
@@ -267,8 +270,16 @@ int b200attn_extend_masked(const void* q, int64_t q_tok_stride, void* out, int64
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */
 #define B200ATTN_EXTEND_MMA 2     /* register-MMA kernel (short / ragged rows, FP8 KV, D == 64) */
-#define B200ATTN_EXTEND_TCGEN05_STEP64 3 /* tcgen05 kernel with S double-buffered in 64-key steps (extend_tc64.cu);
-                                            measured ~equal / slightly slower than TCGEN05 at C3, kept for comparison */
+/* (3 was EXTEND_TCGEN05_STEP64, a 64-key-step variant measured slower at C3 -- 1105 vs 1164 TFLOP/s -- and removed
+ *  in 0.2.0; the result is kept in DESIGN.md) */
+
+/* Validation of a KV-write slot list (debug aid, O(T^2) -- not for the hot path): after the call
+ *   flags[0] = number of pairs t < t' with loc[t] == loc[t'] >= dummy_rows  (a write race: the reference's
+ *              last-writer-wins, memory_pool.py:457-458, is not reproduced for them)
+ *   flags[1] = number of entries outside [0, pool_rows)
+ * flags: 2 int32 on the device.  B200AttnBackend runs it before every KV write when B200ATTN_CHECK_LOC=1. */
+int b200attn_check_loc(const int64_t* loc, int T, int64_t dummy_rows, int64_t pool_rows, int32_t* flags,
+                       b200attn_stream_t stream);
 
 /* ---------------------------------------------------------------- page-table utilities
  * kv_indices[kv_indptr[i] + j] = req_to_token[req_pool_indices[i], kv_start[i] + j], j < lens[i]

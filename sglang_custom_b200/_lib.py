@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
 BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
 SCALE_DIV, SCALE_RCP = 0, 1
-EXTEND_AUTO, EXTEND_TCGEN05, EXTEND_MMA, EXTEND_TCGEN05_STEP64 = 0, 1, 2, 3
+EXTEND_AUTO, EXTEND_TCGEN05, EXTEND_MMA = 0, 1, 2
 WINDOW_NEW_TOKENS_ONLY = -2  # b200attn_extend_masked: no cached-prefix key at all
 ROPE_FP32, ROPE_NATIVE = 0, 1
 LAYOUT_LAYER_FIRST, LAYOUT_PAGE_FIRST, LAYOUT_LAYER_TABLE = 0, 1, 2
@@ -47,6 +47,7 @@ SIGNATURES = {
                              _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _vp, _vp]),
     "b200attn_extend_masked": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
                                     _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
+    "b200attn_check_loc": (_i, [_vp, _i, _i64, _i64, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200attn_transfer_kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),

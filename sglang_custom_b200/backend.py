@@ -70,6 +70,9 @@ class ForwardMetadata:
     # MIXED batches: the running (decode) requests are appended after the prefill requests with
     # extend_len = 1 (schedule_batch.py:1310-1338); that tail is served by the decode kernel
     n_decode_tail: int = 0
+    # number of q rows that belong to the prefill requests (sum of their extend lens, from the host list): the tail
+    # rows start there even when q carries padded rows behind them (DP attention / num_token_non_padded)
+    n_extend_tokens: int = -1
     # TARGET_VERIFY (speculative decoding): every request contributes num_draft_tokens query rows over its
     # seq_lens cached tokens; built on the device, no host sync (triton_backend.py:227-264)
     extend_seq_lens: Optional[torch.Tensor] = None
@@ -125,6 +128,11 @@ class B200AttnBackend(AttentionBackend):
         self.overlap_mixed = 2
         self._side_stream = None
         self.route_decode_tail = True  # MIXED batches: extend_len == 1 tail rows go to the decode kernel
+        # (layer_id, id(forward_batch)) of the last fused RoPE + KV write (rotary.forward_fused_kv): the only case in
+        # which forward_* may be called with k/v and save_kv_cache=False (see _require_kv_in_pool)
+        self._kv_written = None
+        import os
+        self.check_loc = os.environ.get("B200ATTN_CHECK_LOC", "0") not in ("", "0")
 
     # ------------------------------------------------------------------ buffers
     def _alloc_decode_buffers(self, max_bs: int) -> None:
@@ -161,6 +169,7 @@ class B200AttnBackend(AttentionBackend):
             return
         ext_cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
         n_tail = 0
+        t_ext = -1
         if ext_cpu is not None:
             ext_cpu = list(ext_cpu)
             if self.route_decode_tail and self.sliding_window_size is None:
@@ -168,6 +177,7 @@ class B200AttnBackend(AttentionBackend):
                     n_tail += 1
             head = ext_cpu[:len(ext_cpu) - n_tail]
             max_extend = max(head) if head else 0
+            t_ext = int(sum(head))
         else:  # the reference's own (syncing) way, triton_backend.py:320
             max_extend = int(forward_batch.extend_seq_lens.max().item()) if bs else 0
         start = getattr(forward_batch, "extend_start_loc", None)
@@ -178,7 +188,7 @@ class B200AttnBackend(AttentionBackend):
             # a query with extend_len 1 at position L-1 sees all L keys: exactly a decode row
             self._plan_decode(forward_batch.seq_lens[bs - n_tail:])
         self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend,
-                                                n_decode_tail=n_tail)
+                                                n_decode_tail=n_tail, n_extend_tokens=t_ext)
 
     def _plan_decode(self, seq_lens) -> None:
         ops.decode_plan(seq_lens, self.n_ctas, self.plan, self.min_units_per_cta)
@@ -292,11 +302,36 @@ class B200AttnBackend(AttentionBackend):
         vs = getattr(layer, "v_scale_float", None)
         return (1.0 if ks is None else float(ks)), (1.0 if vs is None else float(vs))
 
+    def note_kv_written(self, layer, forward_batch) -> None:
+        """Called by rotary.forward_fused_kv: this layer's new K/V of this batch are already in the pool."""
+        self._kv_written = (layer.layer_id, id(forward_batch))
+
+    def _require_kv_in_pool(self, layer, forward_batch, k) -> None:
+        """save_kv_cache=False contract.  Every key -- cached prefix and new tokens alike -- is read from the paged
+        pool (torch_native_backend.py:196-199 does the same), so with save_kv_cache=False the new tokens must already
+        be there: either the caller passes k=None (the reference's own convention for "KV is in the cache",
+        radix_attention.py:91-99), or rotary.forward_fused_kv wrote them for exactly this layer and batch.  The Triton
+        backend would attend over the passed k/v instead (extend_attention_fwd reads K_Extend/V_Extend); silently
+        reading stale pool rows in that situation is the one thing this must never do."""
+        if k is None or self._kv_written == (layer.layer_id, id(forward_batch)):
+            return
+        raise B200AttnError(
+            "save_kv_cache=False with k/v given, but the new tokens of this layer/batch were not written by "
+            "rotary.forward_fused_kv: the b200 backend reads every key from the paged pool. Pass save_kv_cache=True, "
+            "or k=None if the pool already holds them.")
+
     def _save_kv(self, layer, forward_batch, k, v) -> None:
         pool = forward_batch.token_to_kv_pool
         lid = layer.layer_id - getattr(pool, "start_layer", 0)
         k3 = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
         v3 = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
+        if self.check_loc:  # B200ATTN_CHECK_LOC=1: debug validation, synchronises
+            loc = forward_batch.out_cache_loc
+            dup, oob = ops.check_loc(loc.to(torch.int64).contiguous(), self.page_size, pool.k_buffer[lid].shape[0])
+            if dup or oob:
+                raise B200AttnError(f"out_cache_loc: {dup} duplicate pair(s) outside the dummy page [0, {self.page_size}) "
+                                    f"and {oob} slot(s) out of range -- the reference's last-writer-wins "
+                                    "(memory_pool.py:457-458) is not reproduced for write races")
         # scales are only meaningful when the pool is narrower than k/v (memory_pool.py:436-442);
         # like FlashInfer (flashinfer_backend.py:470-476) the layer's calibrated scales are applied
         ks = getattr(layer, "k_scale", None) if getattr(layer, "k_scale", None) is not None \
@@ -313,6 +348,8 @@ class B200AttnBackend(AttentionBackend):
         o = torch.empty_like(q)
         if save_kv_cache:
             self._save_kv(layer, forward_batch, k, v)
+        else:
+            self._require_kv_in_pool(layer, forward_batch, k)
         if q.shape[0] == 0:
             return o
         md = self.forward_metadata
@@ -336,6 +373,8 @@ class B200AttnBackend(AttentionBackend):
         o = torch.empty_like(q)
         if save_kv_cache:
             self._save_kv(layer, forward_batch, k, v)
+        else:
+            self._require_kv_in_pool(layer, forward_batch, k)
         md = self.forward_metadata
         if md.bs == 0 or q.shape[0] == 0:
             return o
@@ -374,19 +413,20 @@ class B200AttnBackend(AttentionBackend):
                 lse_d = torch.empty((md.bs * nd, Hq), dtype=torch.float32, device=q.device)
                 ops.extend(q3, o_d, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
                            md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, nd, layer.scaling, cap,
-                           k_scale, v_scale, causal=True, kv_dtype=pool.dtype, lse_out=lse_d,
+                           k_scale, v_scale, causal=False, kv_dtype=pool.dtype, lse_out=lse_d,
                            sliding_window_size=_lib.WINDOW_NEW_TOKENS_ONLY, custom_mask=md.custom_mask,
                            mask_indptr=md.mask_indptr)
                 ops.merge_state(o3, lse_p.view(md.bs * nd, Hq), o_d, lse_d, out=o3)
                 return o
             ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
                        md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, md.max_extend_len,
-                       layer.scaling, cap, k_scale, v_scale, causal=causal, kv_dtype=pool.dtype,
+                       layer.scaling, cap, k_scale, v_scale, causal=False, kv_dtype=pool.dtype,
                        custom_mask=md.custom_mask, mask_indptr=md.mask_indptr)
             return o
         n_tail = md.n_decode_tail  # a 1-token row sees all L keys with or without the causal mask
         n_ext = md.bs - n_tail
-        t_ext = q3.shape[0] - n_tail
+        t_ext = md.n_extend_tokens if md.n_extend_tokens >= 0 else q3.shape[0] - n_tail
+        t_end = t_ext + n_tail  # q may carry padded rows behind the tail
         side = None
         if n_tail > 0 and n_ext > 0 and t_ext > 0 and self.overlap_mixed \
                 and not torch.cuda.is_current_stream_capturing():
@@ -401,7 +441,7 @@ class B200AttnBackend(AttentionBackend):
 
             def tail_on_side():
                 with torch.cuda.stream(side):
-                    ops.decode(q3[t_ext:], o3[t_ext:], pool.k_buffer[lid], pool.v_buffer[lid], table,
+                    ops.decode(q3[t_ext:t_end], o3[t_ext:t_end], pool.k_buffer[lid], pool.v_buffer[lid], table,
                                forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan,
                                self.n_ctas, self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)
             if self.overlap_mixed != 2:
@@ -421,7 +461,7 @@ class B200AttnBackend(AttentionBackend):
             # (window layers: a 1-token row's prefix range is its last min(L - 1, W + 1) cached tokens plus itself --
             #  the decode window plan keeps min(L, W + 1); the two differ by one key, so window layers keep the tail
             #  on the extend kernel: route_decode_tail is ignored for them in init_forward_metadata)
-            ops.decode(q3[t_ext:], o3[t_ext:], pool.k_buffer[lid], pool.v_buffer[lid], table,
+            ops.decode(q3[t_ext:t_end], o3[t_ext:t_end], pool.k_buffer[lid], pool.v_buffer[lid], table,
                        forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan, self.n_ctas,
                        self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)
         return o

@@ -9,7 +9,7 @@
 using namespace b200attn;
 
 static int tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
-  return p.tc_variant == 64 ? extend_tc64_launch(p, q_bf16, kvb, st) : extend_tc_launch(p, q_bf16, kvb, st);
+  return extend_tc_launch(p, q_bf16, kvb, st);
 }
 
 static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool,
@@ -37,11 +37,8 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
              B200ATTN_ERR_INVALID, "extend: tensors must be 16-byte aligned");
   B2_REQUIRE(pool_tok_stride >= static_cast<int64_t>(Hkv) * D, B200ATTN_ERR_INVALID, "extend: pool_tok_stride < Hkv*D");
   B2_REQUIRE(k_scale > 0.f && v_scale > 0.f, B200ATTN_ERR_INVALID, "extend: k_scale/v_scale must be > 0");
-  B2_REQUIRE(impl == B200ATTN_EXTEND_AUTO || impl == B200ATTN_EXTEND_TCGEN05 || impl == B200ATTN_EXTEND_MMA ||
-                 impl == B200ATTN_EXTEND_TCGEN05_STEP64,
+  B2_REQUIRE(impl == B200ATTN_EXTEND_AUTO || impl == B200ATTN_EXTEND_TCGEN05 || impl == B200ATTN_EXTEND_MMA,
              B200ATTN_ERR_INVALID, "extend: impl %d", impl);
-  const bool step64 = impl == B200ATTN_EXTEND_TCGEN05_STEP64;
-  if (step64) impl = B200ATTN_EXTEND_TCGEN05;  // same checks and routing from here on
 
   ExtendParams p;
   p.q = q; p.out = out; p.k_pool = k_pool; p.v_pool = v_pool;
@@ -63,9 +60,6 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
     // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
     static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 0; }();
     p.exp_emu = emu;
-    // 128: extend_tc.cu (default, measured faster); 64: extend_tc64.cu (B200ATTN_EXTEND_TCGEN05_STEP64 or the env knob)
-    static const int variant = [] { const char* e = getenv("B200ATTN_EXTEND_TC"); return e ? atoi(e) : 128; }();
-    p.tc_variant = step64 ? 64 : variant;
     static const int order = [] { const char* e = getenv("B200ATTN_GRID_ORDER"); return e ? atoi(e) : 1; }();
     p.grid_order = order;
     static unsigned long long* const prof = [] { const char* e = getenv("B200ATTN_PROF_PTR"); return e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0)) : nullptr; }();

@@ -37,7 +37,6 @@ struct ExtendParams {
   const uint8_t* custom_mask;
   const int64_t* mask_indptr;
   int skip_prefix_mask;
-  int tc_variant;  // 64: extend_tc64.cu (default), 128: extend_tc.cu  (B200ATTN_EXTEND_TC)
   int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 0: measured best at C3)
 };
 
@@ -49,7 +48,5 @@ int extend_mma_masked_launch(const ExtendParams& p, int D, int kvb, bool q_bf16,
 // tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit or FP8-E4M3 KV, logit_cap == 0
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb);
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st);
-// same contract, 64-key-step hand-off (extend_tc64.cu): S double-buffered per Q tile, the softmax warps never wait for S
-int extend_tc64_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st);
 
 }  // namespace b200attn

@@ -34,10 +34,11 @@ template <> struct Vec16<float> {
 };
 
 template <typename T>
-__global__ void __launch_bounds__(256) merge_state_kernel(const T* __restrict__ a, const float* __restrict__ lse_a,
-                                                          const T* __restrict__ b, const float* __restrict__ lse_b,
-                                                          T* __restrict__ out, float* __restrict__ out_lse,
-                                                          int64_t rows, int D) {
+// `out` may alias `a` or `b` (the verify route merges in place, backend.py): every thread loads its own 16 bytes of a
+// and b before it stores them, and none of the three pointers is __restrict__, so the in-place call is well defined.
+__global__ void __launch_bounds__(256) merge_state_kernel(const T* a, const float* __restrict__ lse_a, const T* b,
+                                                          const float* __restrict__ lse_b, T* out,
+                                                          float* __restrict__ out_lse, int64_t rows, int D) {
   using V = Vec16<T>;
   const int vecs = D / V::N;
   const int64_t total = rows * vecs;

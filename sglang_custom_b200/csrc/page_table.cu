@@ -37,9 +37,39 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint8_t* __restr
   }
 }
 
+// Debug check of a KV-write slot list: flags[0] = number of pairs t < t' with loc[t] == loc[t'] >= dummy_rows,
+// flags[1] = number of entries outside [0, pool_rows).  One thread per entry scanning the entries after it: a
+// validation call (O(T^2 / 2) compares of L1/L2-resident data), never on the hot path.
+__global__ void __launch_bounds__(256) check_loc_kernel(const int64_t* __restrict__ loc, int T, int64_t dummy_rows,
+                                                        int64_t pool_rows, int32_t* __restrict__ flags) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const int64_t x = loc[t];
+  if (x < 0 || x >= pool_rows) {
+    atomicAdd(flags + 1, 1);
+    return;
+  }
+  if (x < dummy_rows) return;  // the dummy page soaks up padded rows: duplicates there are the contract
+  int dup = 0;
+  for (int u = t + 1; u < T; ++u) dup += (loc[u] == x);
+  if (dup) atomicAdd(flags, dup);
+}
+
 }  // namespace b200attn
 
 using namespace b200attn;
+
+extern "C" B2_EXPORT int b200attn_check_loc(const int64_t* loc, int T, int64_t dummy_rows, int64_t pool_rows,
+                                            int32_t* flags, b200attn_stream_t stream) {
+  B2_REQUIRE(T >= 0 && dummy_rows >= 0 && pool_rows > 0, B200ATTN_ERR_INVALID, "check_loc: bad sizes");
+  B2_REQUIRE(flags != nullptr && (T == 0 || loc != nullptr), B200ATTN_ERR_INVALID, "check_loc: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  B2_CUDA(cudaMemsetAsync(flags, 0, 2 * sizeof(int32_t), st));
+  if (T == 0) return B200ATTN_OK;
+  check_loc_kernel<<<(T + 255) / 256, 256, 0, st>>>(loc, T, dummy_rows, pool_rows, flags);
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
+}
 
 extern "C" B2_EXPORT int b200attn_flatten_kv_indices(const int32_t* req_to_token, int64_t table_stride,
                                            const void* req_pool_indices, const void* lens, const void* kv_start,

@@ -92,6 +92,8 @@ class Runner:
             q = c.q.reshape(c.T, c.Hq * c.D).to(dev)
             k = c.k_new.reshape(c.T, c.Hkv * c.D).to(dev)
             v = c.v_new.reshape(c.T, c.Hkv * c.D).to(dev)
+        if not save_kv_cache:
+            k = v = None  # "the pool already holds the new tokens" (radix_attention.py:91-99 accepts k=None)
         out = self.layer.forward(q, k, v, fb, save_kv_cache=save_kv_cache)
         torch.cuda.synchronize(dev)
         return out.view(c.T, c.Hq, c.D)

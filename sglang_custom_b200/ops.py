@@ -334,6 +334,19 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
     return out
 
 
+def check_loc(loc: torch.Tensor, dummy_rows: int, pool_rows: int) -> tuple:
+    """(duplicate pairs outside the dummy page, entries out of range) of a KV-write slot list -- a debug check that
+    SYNCHRONISES; see b200attn_check_loc.  The reference is last-writer-wins for duplicates (memory_pool.py:457-458)."""
+    _cuda(loc)
+    if loc.dtype != torch.int64 or not loc.is_contiguous():
+        raise B200AttnError("check_loc: loc must be a contiguous int64 tensor")
+    flags = torch.empty(2, dtype=torch.int32, device=loc.device)
+    check(_lib.load().b200attn_check_loc(loc.data_ptr(), loc.numel(), int(dummy_rows), int(pool_rows),
+                                         flags.data_ptr(), _stream(loc)), "b200attn_check_loc")
+    d, o = flags.tolist()
+    return int(d), int(o)
+
+
 def flatten_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, lens: torch.Tensor,
                        kv_indptr: torch.Tensor, kv_start: Optional[torch.Tensor], kv_indices: torch.Tensor) -> None:
     """create_flashinfer_kv_indices_triton (layers/attention/utils.py:5-41)."""

@@ -6,6 +6,9 @@ same constructor arguments, the same fp32 cos|sin table (`_compute_inv_freq` :10
 `forward(positions, query, key, offsets=None)` contract: query/key are rotated IN PLACE and returned, like the
 reference's CUDA path (`forward_cuda` :218-244 -> sgl-kernel `apply_rope_with_cos_sin_cache_inplace`).
 
+`_compute_inv_freq`, `_compute_cos_sin_cache` and the Llama-3 frequency-scaling formula follow the reference line by
+line on purpose: the cos|sin table has to be bit-identical to the reference's, so there is no second way to write them.
+
 `forward_fused_kv` is the SURVEY 8f rank-2 row: RoPE and `set_kv_buffer` (memory_pool.py:420-458) in one launch; the
 model then calls attention with `save_kv_cache=False` (the hook RadixAttention.forward already has,
 radix_attention.py:82-108).  There is no torch fallback: without libb200attn.so these raise.
@@ -71,6 +74,11 @@ class RotaryEmbedding:
         ops.rope_kv_write(pos, q3, k3, self.cos_sin_cache, self.is_neox_style, v=v3, loc=forward_batch.out_cache_loc,
                           k_pool=pool.k_buffer[lid], v_pool=pool.v_buffer[lid], k_scale=ks, v_scale=vs,
                           pool_dtype=pool.dtype, scale_mode=scale_mode, math_mode=self.math_mode)
+        # tell the backend that this layer's new K/V of this batch are in the pool: forward_*(save_kv_cache=False)
+        # with k/v given raises otherwise (it reads every key from the pool, never from k/v)
+        note = getattr(getattr(forward_batch, "attn_backend", None), "note_kv_written", None)
+        if note is not None:
+            note(layer, forward_batch)
         return query, key
 
 

@@ -47,15 +47,32 @@ def test_library_targets_sm100a_and_uses_blackwell_instructions(lib):
         pytest.skip("cuobjdump not available")
     assert "sm_100a" in res.stdout
     assert "sm_90" not in res.stdout and "sm_80" not in res.stdout
+    # the SASS itself (scripts/dump_sass.py writes the same counts to profiles/r02_sass_summary.txt)
+    import sys
+    sys.path.insert(0, str(ROOT / "scripts"))
+    import dump_sass
+    c = dump_sass.family_counts()
+    tc = c["tc::extend_tc_kernel"]
+    assert tc.get("UTCHMMA", 0) > 0, "extend: no tcgen05.mma (UTCHMMA) in the SASS"
+    assert tc.get("LDTM", 0) > 0 and tc.get("STTM", 0) > 0, "extend: no tcgen05.ld / tcgen05.st (LDTM / STTM)"
+    assert tc.get("UTCBAR", 0) > 0 and tc.get("SYNCS", 0) > 0, "extend: no tcgen05.commit / mbarrier"
+    assert tc.get("LDGSTS", 0) > 0, "extend: the page-1 gather is LDGSTS"
+    assert tc.get("HMMA", 0) == 0 and tc.get("HGMMA", 0) == 0, "extend: legacy tensor path in the tcgen05 kernel"
+    dec = c["decode_kernel"]
+    assert dec.get("LDGSTS", 0) > 0 and dec.get("SYNCS", 0) > 0, "decode: LDGSTS gather + mbarrier hand-off"
+    assert dec.get("HMMA", 0) > 0 and dec.get("LDSM", 0) > 0, "decode: GQA-packed mma.sync from ldmatrix"
+    assert dec.get("F2FP.E4M3", 0) > 0, "decode: FP8 dequantisation in registers"
+    for fam in c:
+        assert c[fam].get("HGMMA", 0) == 0  # wgmma does not exist on sm_100a
 
 
 def test_version_and_error_string(lib):
     from sglang_custom_b200 import _lib
-    assert lib.b200attn_version() == 102
+    assert lib.b200attn_version() == 200
     assert isinstance(lib.b200attn_last_error(), bytes)
     assert lib.b200attn_decode_plan_bytes(256, 148) == 4 * (8 + 257 + 148)
     assert lib.b200attn_decode_workspace_bytes(148, 32, 128) == 2 * 148 * 32 * 129 * 4
-    assert _lib.version() == 102
+    assert _lib.version() == 200
 
 
 def test_argument_validation_returns_error_codes_without_a_device(lib):

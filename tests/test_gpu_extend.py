@@ -64,7 +64,7 @@ def _direct(case, device, kp, vp, impl, causal=True, logit_cap=0.0, want_lse=Fal
     return (out, lse) if want_lse else out
 
 
-@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05, _lib.EXTEND_TCGEN05_STEP64])
+@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05])
 @pytest.mark.parametrize("lens,ext", [([512, 300], [256, 300]), ([129], [129]), ([2048 + 64], [64]), ([1000, 1, 260], [999, 1, 130])])
 def test_both_extend_kernels_agree_with_fp64(impl, lens, ext, device):
     case = synth.make_case(len(lens), 8, 2, 128, lens, extend_lens=ext, seed=sum(lens))
@@ -75,7 +75,7 @@ def test_both_extend_kernels_agree_with_fp64(impl, lens, ext, device):
     assert torch.allclose(lse.cpu(), want_lse, atol=2e-3, rtol=1e-4)
 
 
-@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05, _lib.EXTEND_TCGEN05_STEP64])
+@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05])
 @pytest.mark.parametrize("kw", [dict(kv_scale=1.0), dict(kv_scale=0.1135), dict(kv_scale=0.1135, page_size=16),
                                 dict(kv_scale=0.5, dtype=torch.float16)])
 def test_fp8_kv_extend_both_kernels(impl, kw, device):
@@ -92,7 +92,7 @@ def test_fp8_kv_extend_both_kernels(impl, kw, device):
     H.assert_close(out, H.oracle_extend(case, kp, vp), what="fp8 vs torch_native on the dequantised pool")
 
 
-@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05, _lib.EXTEND_TCGEN05_STEP64])
+@pytest.mark.parametrize("impl", [_lib.EXTEND_MMA, _lib.EXTEND_TCGEN05])
 def test_extend_non_causal_encoder_only(impl, device):
     """ENCODER_ONLY layers attend bidirectionally (torch_native_backend.py:206-208)."""
     case = synth.make_case(2, 8, 2, 128, [200, 131], extend_lens=[200, 131], seed=9)
