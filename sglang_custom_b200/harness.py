@@ -23,17 +23,24 @@ class Runner:
     RadixAttention.forward -> backend.forward_decode / forward_extend -> C ABI."""
 
     def __init__(self, case, device, max_reqs: Optional[int] = None, sliding_window_size: Optional[int] = None,
-                 num_draft_tokens: Optional[int] = None):
+                 num_draft_tokens: Optional[int] = None, tp_size: int = 1, tp_rank: int = 0):
+        """tp_size > 1: `case` is rank tp_rank's slice (synth.make_case_device(head_shard=...) / tp.shard_case) of a
+        model with case.Hq * tp_size query heads; the ModelRunner stand-in is built with the GLOBAL head counts and
+        tp_size, and the backend derives its per-rank heads from them as TritonAttnBackend does
+        (triton_backend.py:69-76)."""
         from sglang_custom_b200 import interfaces as itf
         from sglang_custom_b200.backend import B200AttnBackend
         self.itf = itf
         self.case = case
         self.device = device
         kv_dtype = torch.float8_e4m3fn if case.fp8 else case.dtype
-        cfg = itf.ModelConfig(context_len=case.req_to_token.shape[1], num_attention_heads=case.Hq,
-                              num_key_value_heads=case.Hkv, head_dim=case.D, num_hidden_layers=1)
+        hkv_global = getattr(case, "Hkv_global", case.Hkv * tp_size)
+        cfg = itf.ModelConfig(context_len=case.req_to_token.shape[1], num_attention_heads=case.Hq * tp_size,
+                              num_key_value_heads=hkv_global, head_dim=case.D, num_hidden_layers=1)
         self.mr = itf.ModelRunner(cfg, max_reqs=case.req_to_token.shape[0], pool_size=case.P - case.page_size,
-                                  device=str(device), kv_dtype=kv_dtype, page_size=case.page_size, dtype=case.dtype)
+                                  device=str(device), kv_dtype=kv_dtype, page_size=case.page_size, dtype=case.dtype,
+                                  tp_size=tp_size, tp_rank=tp_rank)
+        assert cfg.get_num_kv_heads(tp_size) == case.Hkv, "case is not this rank's KV-head slice"
         self.mr.req_to_token_pool.req_to_token.copy_(case.req_to_token.to(device))
         pool = self.mr.token_to_kv_pool
         pool.k_buffer[0].copy_(case.k_pool.to(device))

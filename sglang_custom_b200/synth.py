@@ -154,10 +154,26 @@ def make_case_device(bs: int, Hq: int, Hkv: int, D: int, seq_lens: Sequence[int]
                      extend_lens: Optional[Sequence[int]] = None, page_size: int = 1, fp8: bool = False,
                      kv_scale: float = 1.0, seed: int = BASELINE_SEED, table: str = "permuted",
                      idx_dtype: torch.dtype = torch.int64, dtype: torch.dtype = torch.bfloat16,
-                     pool_rows: Optional[int] = None) -> types.SimpleNamespace:
+                     pool_rows: Optional[int] = None, head_shard: Optional[tuple] = None) -> types.SimpleNamespace:
     """Same layout as make_case, generated with the device's RNG so BASELINE-size pools (GiBs) never cross PCIe.
-    The pool state is AFTER-write-agnostic: rows of the new tokens hold random data that the forward overwrites."""
+    The pool state is AFTER-write-agnostic: rows of the new tokens hold random data that the forward overwrites.
+
+    head_shard = (rank, world): build only rank's slice of the GLOBAL case with Hq / Hkv heads, partitioned the way
+    SGLang tensor parallelism does (models/llama.py:118-131; KV heads replicated when world > Hkv,
+    model_config.py:342-349).  Every head is drawn from its own generator (seeded by the global head index), so
+    the concatenation of the ranks' slices is one and the same global case whatever `world` is -- including
+    world = 1 -- and no rank ever materialises more than its slice.  The page table is identical on every rank."""
     dev = torch.device(device)
+    q_ids = kv_ids = None
+    if head_shard is not None:
+        rank, world = head_shard
+        assert Hq % world == 0 and (Hkv % world == 0 or world % Hkv == 0), "tp must divide / be a multiple of Hkv"
+        hq_l, hkv_l = Hq // world, max(1, Hkv // world)
+        q_ids = list(range(rank * hq_l, (rank + 1) * hq_l))
+        kv0 = rank * hkv_l if Hkv % world == 0 else rank // (world // Hkv)
+        kv_ids = list(range(kv0, kv0 + hkv_l))
+        hkv_global = Hkv
+        Hq, Hkv = hq_l, hkv_l
     gen = torch.Generator(device=dev).manual_seed(seed)
     cpu_gen = torch.Generator().manual_seed(seed)
     seq = torch.as_tensor(list(seq_lens), dtype=torch.int64)
@@ -183,16 +199,23 @@ def make_case_device(bs: int, Hq: int, Hkv: int, D: int, seq_lens: Sequence[int]
         req_to_token[req_rows[i], :npg * page_size] = slots.to(torch.int32)
         off += npg
 
-    def rnd(shape):
+    def rnd(shape, ids=None, salt=0):
         out = torch.empty(shape, dtype=dtype, device=dev)
-        flat = out.view(shape[0], -1)
         step = 1 << 18
-        for r0 in range(0, shape[0], step):
-            r1 = min(shape[0], r0 + step)
-            flat[r0:r1] = torch.randn((r1 - r0, flat.shape[1]), generator=gen, device=dev, dtype=torch.float32).to(dtype)
+        if ids is None:
+            flat = out.view(shape[0], -1)
+            for r0 in range(0, shape[0], step):
+                r1 = min(shape[0], r0 + step)
+                flat[r0:r1] = torch.randn((r1 - r0, flat.shape[1]), generator=gen, device=dev, dtype=torch.float32).to(dtype)
+            return out
+        for j, h in enumerate(ids):  # one generator per GLOBAL head: the data do not depend on the partition
+            gh = torch.Generator(device=dev).manual_seed(seed * 1_000_003 + salt * 10_007 + h)
+            for r0 in range(0, shape[0], step * 4):
+                r1 = min(shape[0], r0 + step * 4)
+                out[r0:r1, j] = torch.randn((r1 - r0, shape[2]), generator=gh, device=dev, dtype=torch.float32).to(dtype)
         return out
 
-    k_pool, v_pool = rnd((P, Hkv, D)), rnd((P, Hkv, D))
+    k_pool, v_pool = rnd((P, Hkv, D), kv_ids, 1), rnd((P, Hkv, D), kv_ids, 2)
     k_pool[:page_size] = 0
     v_pool[:page_size] = 0
     if fp8:
@@ -206,8 +229,8 @@ def make_case_device(bs: int, Hq: int, Hkv: int, D: int, seq_lens: Sequence[int]
                 out[r0:r0 + step] = y.to(torch.float8_e4m3fn).view(torch.uint8)
             return out
         k_pool, v_pool = quant(k_pool), quant(v_pool)
-    q = rnd((max(T, 1), Hq, D))[:T]
-    k_new, v_new = rnd((max(T, 1), Hkv, D))[:T], rnd((max(T, 1), Hkv, D))[:T]
+    q = rnd((max(T, 1), Hq, D), q_ids, 3)[:T]
+    k_new, v_new = rnd((max(T, 1), Hkv, D), kv_ids, 4)[:T], rnd((max(T, 1), Hkv, D), kv_ids, 5)[:T]
     prefix = seq - ext
     start = torch.cumsum(ext, 0) - ext
     loc = torch.cat([req_to_token[req_rows[i], int(prefix[i]):int(seq[i])].to(torch.int64) for i in range(bs)]) \
@@ -218,7 +241,19 @@ def make_case_device(bs: int, Hq: int, Hkv: int, D: int, seq_lens: Sequence[int]
         req_to_token=req_to_token.to(dev), req_pool_indices=req_rows.to(idx_dtype).to(dev),
         seq_lens=seq.to(idx_dtype).to(dev), out_cache_loc=loc.to(dev), extend_seq_lens=ext.to(torch.int32).to(dev),
         extend_prefix_lens=prefix.to(torch.int32).to(dev), extend_start_loc=start.to(torch.int32).to(dev),
-        max_extend_len=int(ext.max()) if bs else 0, seq_lens_sum=int(seq.sum()))
+        max_extend_len=int(ext.max()) if bs else 0, seq_lens_sum=int(seq.sum()),
+        Hkv_global=hkv_global if head_shard is not None else Hkv)
+
+
+def c5_lengths(seed: int = 5, scale: int = 1) -> tuple:
+    """BASELINE configs[4]: one MIXED forward of 8 chunked-prefill rows (prefix 16 * U[0, 1536), chunk
+    1024) followed by 248 running decode rows with L ~ U[1024, 32768].  `scale` divides counts and lengths for tests.
+    Returns (seq_lens, extend_lens, n_extend_rows)."""
+    g = torch.Generator().manual_seed(seed)
+    n_dec, n_ext, E = 248 // scale, max(1, 8 // scale), 1024 // scale
+    ext_prefix = (16 * torch.randint(0, max(1, 1536 // scale), (n_ext,), generator=g)).tolist()
+    dec_lens = torch.randint(1024 // scale, 32768 // scale + 1, (n_dec,), generator=g).tolist()
+    return [p + E for p in ext_prefix] + dec_lens, [E] * n_ext + [1] * n_dec, n_ext
 
 
 def extract_subcase(case: types.SimpleNamespace, req_ids: Sequence[int], k_pool=None, v_pool=None) -> types.SimpleNamespace:

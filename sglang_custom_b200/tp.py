@@ -64,6 +64,50 @@ def gather_heads(out_local: torch.Tensor, world: int) -> torch.Tensor:
     return torch.cat(parts, dim=1)
 
 
+def _gather_device():
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+
+
+def gather_cat(t: torch.Tensor, world: int, dim: int = 1) -> torch.Tensor:
+    """Concatenate equally shaped per-rank tensors along `dim` in rank order; the result is a CPU tensor on every
+    rank (harness-only collective, used to rebuild a GLOBAL sample for the parity check)."""
+    if world == 1:
+        return t.cpu()
+    x = t.contiguous().to(_gather_device())
+    if x.dtype == torch.float8_e4m3fn:
+        x = x.view(torch.uint8)
+    parts: List[torch.Tensor] = [torch.empty_like(x) for _ in range(world)]
+    dist.all_gather(parts, x)
+    return torch.cat(parts, dim=dim).cpu()
+
+
+def gather_subcase(sub, world: int, kv_replicas: int = 1):
+    """Per-rank CPU sub-cases (synth.extract_subcase of the same requests on every rank's head slice) -> the GLOBAL
+    sub-case: q / k_new / v_new / pools concatenated over heads in rank order (= SGLang's head order,
+    models/llama.py:118-131).  With replicated KV heads (world > Hkv) every `kv_replicas`-th rank contributes its KV."""
+    if world == 1:
+        return sub
+    import types
+    out = types.SimpleNamespace(**vars(sub))
+    out.q = gather_cat(sub.q, world)
+    for name in ("k_new", "v_new", "k_pool", "v_pool"):
+        full = gather_cat(getattr(sub, name), world)
+        if kv_replicas > 1:  # [.., world * 1, D]: keep one copy per KV head
+            full = full[:, ::kv_replicas].contiguous()
+        setattr(out, name, full)
+    out.Hq = out.q.shape[1]
+    out.Hkv = out.k_pool.shape[1]
+    return out
+
+
+def all_true(flag: bool, world: int, device="cpu") -> bool:
+    if world == 1:
+        return bool(flag)
+    t = torch.tensor([1.0 if flag else 0.0], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item() > 0.5)
+
+
 def barrier(world: int) -> None:
     if world > 1:
         dist.barrier()

@@ -129,3 +129,49 @@ def test_tp2_gloo_partition_gather_and_max_timing():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert ok and t_max == 2.0 and t_sum == 3.0
+
+
+def _tp_subcase_worker(rank: int, world: int, port: int, q):
+    """The bench.py / test_gpu_tp.py parity path with the per-rank attention replaced by the oracle on the rank's
+    slice: head-sharded generation, extract_subcase on every rank, all-gather of the sample into the GLOBAL sub-case."""
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    r, w, _ = tp.init("gloo")
+    lens, ext = [40, 7, 25, 33], [5, 7, 1, 1]
+    local = synth.make_case_device(4, 8, 2, 64, lens, "cpu", extend_lens=ext, seed=21, head_shard=(r, w))
+    assert local.Hq == 8 // w and local.Hkv == max(1, 2 // w) and local.Hkv_global == 2
+    kp, vp = H.pool_after_write(local)
+    out_local = tn.extend(local.q, kp, vp, local.req_to_token, local.req_pool_indices, local.seq_lens,
+                          local.extend_prefix_lens, local.extend_seq_lens, local.sm_scale)
+    sample = [0, 2, 3]
+    sub = synth.extract_subcase(local, sample, kp, vp)
+    gsub = tp.gather_subcase(sub, w, kv_replicas=max(1, w // 2))
+    got = tp.gather_cat(out_local[sub.token_rows], w)
+    ok_all = tp.all_true(r != 1, w)  # rank 1 votes False
+    if r == 0:
+        full = synth.make_case_device(4, 8, 2, 64, lens, "cpu", extend_lens=ext, seed=21, head_shard=(0, 1))
+        fk, fv = H.pool_after_write(full)
+        fsub = synth.extract_subcase(full, sample, fk, fv)
+        same = all(torch.equal(getattr(gsub, n), getattr(fsub, n)) for n in ("q", "k_new", "v_new", "k_pool", "v_pool"))
+        want = H.oracle_extend(gsub, gsub.k_pool, gsub.v_pool)
+        q.put((same, bool(torch.equal(got, want)), gsub.Hq, gsub.Hkv, ok_all))
+    tp.barrier(w)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_tp_gloo_head_sharded_generation_and_global_subcase(world):
+    """world 2 (KV heads split) and 4 (world > Hkv: KV heads replicated, Q heads split): the ranks' slices are one
+    global case whatever the world size, and the gathered sample equals the world-1 sample bit for bit."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_tp_subcase_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    same, ok, hq, hkv, all_ok = q.get(timeout=180)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert same and ok and (hq, hkv) == (8, 2) and all_ok is False
