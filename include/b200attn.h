@@ -21,6 +21,8 @@
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
  *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
  *   b200attn_decode_multiq       cached-prefix part of TARGET_VERIFY batches (triton_backend.py:227-264)
+ *   b200attn_decode_paged, b200attn_decode_multiq_paged, b200attn_extend_paged
+ *                                the same three for paged pools (mem_cache/allocator.py:444-447 slot layout)
  *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
  *   b200attn_extend_masked       triton_ops/extend_attention.py:158-175,236-247 (sliding window, custom mask)
  *   b200attn_check_loc           mem_cache/memory_pool.py:457-458 (`buf[loc] = x`: which duplicates are legal)
@@ -49,7 +51,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_VERSION 200 /* 0.2.0: + check_loc; EXTEND_TCGEN05_STEP64 removed */
+#define B200ATTN_VERSION 210 /* 0.2.1: + decode_paged / decode_multiq_paged / extend_paged (page_size >= 16: TMA box loads) */
 
 /* element types */
 #define B200ATTN_BF16 0
@@ -209,6 +211,32 @@ int b200attn_decode_multiq(const void* q, int64_t q_req_stride, int64_t q_tok_st
                            float v_scale, const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
                            float* lse_out, int64_t lse_req_stride, b200attn_stream_t stream);
 
+/* Paged pools (page_size > 1).  SGLang's paged allocator hands out pages of page_size consecutive slots
+ * (mem_cache/allocator.py:444-447: `out_pages[:, None] * page_size + arange(page_size)`) and position p of a request
+ * sits at req_to_token[r, p] = page(p / page_size) * page_size + p % page_size, so the 16 rows of every 16-token unit
+ * [16 j, 16 j + 16) of a request are 16 CONSECUTIVE pool rows when page_size % 16 == 0.  These entry points take the
+ * page size; with page_size % 16 == 0 and D = 128 the producers read ONE table entry per unit and fetch the unit's K
+ * and V rows as bulk-tensor (TMA, cp.async.bulk.tensor with 128-byte swizzle) boxes instead of 16 row gathers.  Any
+ * other page_size runs the row-gather kernel of b200attn_decode; results are identical either way.
+ *   stage: 0 = b200attn_decode (stage 1 + merge), 1 = b200attn_decode_partial (stage 1 only)
+ * Contract: the consecutive-slot layout above (the caller asserts it by passing page_size > 1), and a plan from
+ * b200attn_decode_plan (a sliding-window plan shifts requests off their page boundary: pass page_size = 1 there). */
+int b200attn_decode_paged(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                          const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                          const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                          const void* seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype,
+                          int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
+                          const int32_t* plan, int n_ctas, void* workspace, size_t workspace_bytes,
+                          float* lse_out, int page_size, int stage, b200attn_stream_t stream);
+int b200attn_decode_multiq_paged(const void* q, int64_t q_req_stride, int64_t q_tok_stride, void* out,
+                                 int64_t out_req_stride, int64_t out_tok_stride, const void* k_pool,
+                                 const void* v_pool, int64_t pool_tok_stride, const int32_t* req_to_token,
+                                 int64_t table_stride, const void* req_pool_indices, const void* seq_lens,
+                                 int idx_is_i64, int bs, int nq, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,
+                                 float sm_scale, float logit_cap, float k_scale, float v_scale, const int32_t* plan,
+                                 int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
+                                 int64_t lse_req_stride, int page_size, b200attn_stream_t stream);
+
 /* ---------------------------------------------------------------- 2-way LSE merge
  * out = (e^{la-m} a + e^{lb-m} b) / (e^{la-m} + e^{lb-m}),  lse = log(sum) + m, m = max(la, lb);
  * +inf LSE is treated as -inf (merge_attn_states.cu:47-50).
@@ -266,6 +294,21 @@ int b200attn_extend_masked(const void* q, int64_t q_tok_stride, void* out, int64
                            float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
                            const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask,
                            float* lse_out, b200attn_stream_t stream);
+
+/* b200attn_extend_masked for a paged pool (contract as b200attn_decode_paged; sliding_window_size = -1 and
+ * custom_mask = NULL give plain b200attn_extend).  With page_size % 16 == 0 and a 16-bit pool the tcgen05 kernel's
+ * producer reads one table entry per 16-key page and fetches the page as two bulk-tensor (TMA) boxes of
+ * 16 rows x 128 B whose 128-byte swizzle is the UMMA operand layout; FP8 pools keep the register-expanding
+ * producers, the register-MMA kernel keeps its row gathers.  Results are identical to page_size = 1. */
+int b200attn_extend_paged(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                           const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                           const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                           const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
+                           const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
+                           int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                           float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
+                           const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask,
+                           float* lse_out, int page_size, b200attn_stream_t stream);
 #define B200ATTN_WINDOW_NEW_TOKENS_ONLY (-2)
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */

@@ -69,7 +69,7 @@ def main():
         run("C2 page16", 256, 32, 8, 128, [4096] * 256, False, (148,), page_size=16)
         run("C2 arange table (sequential slots)", 256, 32, 8, 128, [4096] * 256, False, (148,), table="arange")
     if which in ("all", "c4"):
-        for tp, (hq, hkv) in ((2, (32, 4)), (4, (16, 2)), (8, (8, 1))):
+        for tp, (hq, hkv) in ((1, (64, 8)), (2, (32, 4)), (4, (16, 2)), (8, (8, 1))):
             run(f"C4 fp8 tp{tp} {hq}/{hkv} bs512 ctx8192", 512, hq, hkv, 128, [8192] * 512, True, (148, 296))
     if which in ("all", "c4layout"):  # how much of the FP8 / 1-KV-head gap is DRAM row locality (128-byte random rows)
         run("C4 fp8 tp8 8/1 arange table", 512, 8, 1, 128, [8192] * 512, True, (148,), table="arange")

@@ -41,12 +41,19 @@ SIGNATURES = {
                                      _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _vp]),
     "b200attn_decode_multiq": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i,
                                     _i, _i, _i, _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _i64, _vp]),
+    "b200attn_decode_paged": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i,
+                                   _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _i, _i, _vp]),
+    "b200attn_decode_multiq_paged": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i,
+                                          _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _i64, _i,
+                                          _vp]),
     "b200attn_decode_merge": (_i, [_vp, _i64, _i, _i, _i, _i, _vp, _i, _vp, _sz, _vp, _vp]),
     "b200attn_merge_state": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b200attn_extend": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
                              _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _vp, _vp]),
     "b200attn_extend_masked": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
                                     _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
+    "b200attn_extend_paged": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
+                                   _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _i, _vp, _i, _vp]),
     "b200attn_check_loc": (_i, [_vp, _i, _i64, _i64, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),

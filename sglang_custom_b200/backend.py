@@ -81,6 +81,11 @@ class ForwardMetadata:
     custom_mask: Optional[torch.Tensor] = None
     mask_indptr: Optional[torch.Tensor] = None
     prefix_seq_lens: Optional[torch.Tensor] = None  # = forward_batch.seq_lens of a verify batch (its own dtype)
+    # DRAFT_EXTEND (speculative decoding): accept_length[i] new tokens at the end of seq_lens[i], plain causal extend
+    draft_extend: bool = False
+    # a draft decode step (B200MultiStepDraftBackend): the rows read their keys through this table instead of the
+    # pool's req_to_token (topk > 1: a per-branch copy with the branch's draft tokens behind the shared prefix)
+    req_to_token: Optional[torch.Tensor] = None
 
 
 class B200AttnBackend(AttentionBackend):
@@ -100,6 +105,7 @@ class B200AttnBackend(AttentionBackend):
         self.sliding_window_size = int(sw) if sw is not None and sw > 0 else None
         sargs = getattr(model_runner, "server_args", None)
         self.num_draft_tokens = getattr(sargs, "speculative_num_draft_tokens", None)
+        self.speculative_num_steps = getattr(sargs, "speculative_num_steps", None)
         if getattr(model_runner.model_config, "is_encoder_decoder", False):
             raise NotImplementedError("b200 attention backend: encoder-decoder (cross attention) is not built")
 
@@ -156,12 +162,21 @@ class B200AttnBackend(AttentionBackend):
         mode = forward_batch.forward_mode
         spec_info = getattr(forward_batch, "spec_info", None)
         if spec_info is not None:
-            if not (hasattr(mode, "is_target_verify") and mode.is_target_verify()):
-                raise NotImplementedError("b200 attention backend: of the speculative-decoding modes only "
-                                          "TARGET_VERIFY is built (no DRAFT_EXTEND / multi-step draft decode)")
-            self.forward_metadata = self._verify_metadata(len(forward_batch.req_pool_indices), forward_batch.seq_lens,
-                                                          spec_info, None)
-            return
+            if hasattr(mode, "is_target_verify") and mode.is_target_verify():
+                self.forward_metadata = self._verify_metadata(len(forward_batch.req_pool_indices),
+                                                              forward_batch.seq_lens, spec_info, None)
+                return
+            if hasattr(mode, "is_draft_extend") and mode.is_draft_extend():
+                self.forward_metadata = self._draft_extend_metadata(len(forward_batch.req_pool_indices),
+                                                                    forward_batch.seq_lens, spec_info, None)
+                return
+            if mode.is_decode_or_idle():
+                # a draft decode step: rows, lengths and table come from B200MultiStepDraftBackend
+                # (the reference hands kv_indptr / kv_indices over the same way, triton_backend.py:203-205)
+                self.forward_metadata = self._draft_step_metadata(spec_info)
+                return
+            # EXTEND with a spec_info attached (the draft model's own prefill, eagle_worker.py forward_draft_extend):
+            # attention-wise a plain extend batch -- the Triton backend takes its default branch for it too
         if mode.is_decode_or_idle():
             if bs > 0:
                 self._plan_decode(forward_batch.seq_lens)
@@ -195,6 +210,43 @@ class B200AttnBackend(AttentionBackend):
         if self.window_plan is not None:
             ops.decode_plan(seq_lens, self.n_ctas, self.window_plan, self.min_units_per_cta,
                             sliding_window_size=self.sliding_window_size)
+
+    def _draft_step_metadata(self, spec_info) -> ForwardMetadata:
+        step = getattr(spec_info, "b200_draft_step", None)
+        if step is None:
+            raise B200AttnError("decode batch with a spec_info but no draft-step rows: draft decoding runs through "
+                                "B200MultiStepDraftBackend (draft_backend.py), as TritonMultiStepDraftBackend does")
+        rows, lens, table = step
+        if rows.numel() > 0:
+            self._plan_decode(lens)
+        return ForwardMetadata(True, rows.numel(), req_pool_indices=rows, seq_lens=lens, req_to_token=table)
+
+    def _draft_extend_metadata(self, bs: int, seq_lens, spec_info, bufs) -> ForwardMetadata:
+        """DRAFT_EXTEND (eagle_utils.py:107-133): after a verify step the draft model extends every request by its
+        accept_length[i] (already + 1) accepted tokens; forward_batch.seq_lens INCLUDES them.  Query t of request i
+        sits at position seq_lens[i] - accept_length[i] + t and sees the keys up to itself -- the semantics of the
+        reference's default (FlashInfer) backend: qo_indptr = cumsum(accept_length), paged_kernel_lens = seq_lens,
+        causal (flashinfer_backend.py prefill updater; eagle_utils.py:135-164).  The reference's Triton backend hands
+        the SAME key range to its extend kernel as an unmasked prefix and then adds the new tokens a second time
+        under the causal mask (triton_backend.py:265-281 + extend_attention.py stage 1 / stage 2), i.e. it counts the
+        accepted tokens twice; that quirk is not reproduced.
+        No host sync: the grid is sized by speculative_num_steps + 1 (the reference's own bound under CUDA graphs,
+        triton_backend.py:476-499) instead of max(accept_length).item()."""
+        acc = spec_info.accept_length[:bs].to(torch.int32)
+        sl = seq_lens[:bs]
+        steps = self.speculative_num_steps
+        max_ext = int(steps) + 1 if steps else (int(acc.max().item()) if bs else 0)
+        if bufs is None:
+            ext = acc.contiguous()
+            prefix = (sl.to(torch.int32) - acc).contiguous()
+            start = (torch.cumsum(acc, 0, dtype=torch.int32) - acc).contiguous()
+        else:
+            ext, prefix, start = bufs[0][:bs], bufs[1][:bs], bufs[2][:bs]
+            ext.copy_(acc)
+            prefix.copy_(sl.to(torch.int32) - acc)
+            start.copy_(torch.cumsum(acc, 0, dtype=torch.int32) - acc)
+        return ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_ext, extend_seq_lens=ext,
+                               extend_prefix_lens=prefix, total_lens=sl, draft_extend=True)
 
     def _verify_metadata(self, bs: int, seq_lens, spec_info, bufs) -> ForwardMetadata:
         """TARGET_VERIFY (triton_backend.py:227-264): qo_indptr = arange * num_draft_tokens, the prefix is seq_lens
@@ -237,6 +289,9 @@ class B200AttnBackend(AttentionBackend):
         if max_bs > self.max_bs:
             self.max_bs = max_bs
             self._alloc_decode_buffers(max_bs)
+        if self.speculative_num_steps and not self.skip_prefill:
+            i32 = dict(dtype=torch.int32, device=self.device)
+            self.cg_draft_extend = (torch.zeros(max_bs, **i32), torch.zeros(max_bs, **i32), torch.zeros(max_bs, **i32))
         if self.num_draft_tokens and not self.skip_prefill:
             # TARGET_VERIFY graphs: fixed-address lens / mask buffers (triton_backend.py:366-371)
             i32 = dict(dtype=torch.int32, device=self.device)
@@ -260,7 +315,21 @@ class B200AttnBackend(AttentionBackend):
             md.req_pool_indices = req_pool_indices[:bs]
             self.forward_metadata = md
             return
-        raise NotImplementedError("b200 attention backend: only DECODE and TARGET_VERIFY batches run under CUDA graphs")
+        if hasattr(forward_mode, "is_draft_extend") and forward_mode.is_draft_extend() and spec_info is not None:
+            # triton_backend.py:476-499: captured with speculative_num_steps + 1 rows per request; the replay hook
+            # refills the same buffers from accept_length (:609-625)
+            if getattr(self, "cg_draft_extend", None) is None:
+                raise B200AttnError("DRAFT_EXTEND capture before init_cuda_graph_state / without speculative_num_steps")
+            md = self._draft_extend_metadata(bs, seq_lens, spec_info, self.cg_draft_extend)
+            md.req_pool_indices = req_pool_indices[:bs]
+            md.total_lens = seq_lens[:bs]
+            self.forward_metadata = md
+            return
+        if forward_mode.is_decode_or_idle() and spec_info is not None:
+            self.forward_metadata = self._draft_step_metadata(spec_info)  # fixed buffers owned by the multi-step backend
+            return
+        raise NotImplementedError(f"b200 attention backend: {forward_mode!r} does not run under CUDA graphs "
+                                  "(the reference raises for it too, triton_backend.py:503-506)")
 
     def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens,
                                                 forward_mode, spec_info, seq_lens_cpu):
@@ -272,7 +341,14 @@ class B200AttnBackend(AttentionBackend):
         if hasattr(forward_mode, "is_target_verify") and forward_mode.is_target_verify() and spec_info is not None:
             self._verify_metadata(bs, seq_lens, spec_info, self.cg_verify)  # refills the captured buffers in place
             return
-        raise NotImplementedError("b200 attention backend: only DECODE and TARGET_VERIFY batches run under CUDA graphs")
+        if hasattr(forward_mode, "is_draft_extend") and forward_mode.is_draft_extend() and spec_info is not None:
+            self._draft_extend_metadata(bs, seq_lens, spec_info, self.cg_draft_extend)
+            return
+        if forward_mode.is_decode_or_idle() and spec_info is not None:
+            self._draft_step_metadata(spec_info)  # re-plans over the step's (in place refreshed) lengths
+            return
+        raise NotImplementedError(f"b200 attention backend: {forward_mode!r} does not run under CUDA graphs "
+                                  "(the reference raises for it too, triton_backend.py:627-630)")
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
@@ -364,8 +440,12 @@ class B200AttnBackend(AttentionBackend):
         plan = self.window_plan if self._layer_window(layer) > -1 else self.plan
         ops.decode(q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
                    o.view(-1, layer.tp_q_head_num, layer.v_head_dim), pool.k_buffer[lid], pool.v_buffer[lid],
-                   forward_batch.req_to_token_pool.req_to_token, rpi, sl, plan, self.n_ctas, self.workspace,
-                   layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0, k_scale, v_scale, kv_dtype=pool.dtype)
+                   md.req_to_token if md.req_to_token is not None else forward_batch.req_to_token_pool.req_to_token,
+                   rpi, sl, plan, self.n_ctas, self.workspace,
+                   layer.scaling, getattr(layer, "logit_cap", 0.0) or 0.0, k_scale, v_scale, kv_dtype=pool.dtype,
+                   # paged pools: 16-token units are TMA boxes (a window plan starts requests off their page boundary)
+                   # a draft step's branch table is a copy with the draft tokens spliced in: row gathers
+                   page_size=self.page_size if (plan is self.plan and md.req_to_token is None) else 1)
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
@@ -408,20 +488,29 @@ class B200AttnBackend(AttentionBackend):
                     ops.decode_multiq(q4[:, t0:t0 + per_pass], o4[:, t0:t0 + per_pass], pool.k_buffer[lid],
                                       pool.v_buffer[lid], table, rpi, md.prefix_seq_lens, self.plan, self.n_ctas,
                                       self.verify_workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype,
-                                      lse_out=lse_p[:, t0:t0 + per_pass])
+                                      lse_out=lse_p[:, t0:t0 + per_pass], page_size=self.page_size)
                 o_d = torch.empty_like(o3)
                 lse_d = torch.empty((md.bs * nd, Hq), dtype=torch.float32, device=q.device)
                 ops.extend(q3, o_d, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
                            md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, nd, layer.scaling, cap,
                            k_scale, v_scale, causal=False, kv_dtype=pool.dtype, lse_out=lse_d,
                            sliding_window_size=_lib.WINDOW_NEW_TOKENS_ONLY, custom_mask=md.custom_mask,
-                           mask_indptr=md.mask_indptr)
+                           mask_indptr=md.mask_indptr, page_size=self.page_size)
                 ops.merge_state(o3, lse_p.view(md.bs * nd, Hq), o_d, lse_d, out=o3)
                 return o
             ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi, md.total_lens,
                        md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, md.max_extend_len,
                        layer.scaling, cap, k_scale, v_scale, causal=False, kv_dtype=pool.dtype,
-                       custom_mask=md.custom_mask, mask_indptr=md.mask_indptr)
+                       custom_mask=md.custom_mask, mask_indptr=md.mask_indptr, page_size=self.page_size)
+            return o
+        if md.draft_extend:
+            if window > -1:
+                raise NotImplementedError("b200 attention backend: sliding window with speculative decoding")
+            rpi = md.req_pool_indices if md.req_pool_indices is not None else forward_batch.req_pool_indices
+            ops.extend(q3, o3, pool.k_buffer[lid], pool.v_buffer[lid], table, rpi[:md.bs], md.total_lens,
+                       md.extend_seq_lens, md.extend_prefix_lens, md.extend_start_loc, md.max_extend_len,
+                       layer.scaling, cap, k_scale, v_scale, causal=causal, kv_dtype=pool.dtype,
+                       page_size=self.page_size)
             return o
         n_tail = md.n_decode_tail  # a 1-token row sees all L keys with or without the causal mask
         n_ext = md.bs - n_tail
@@ -443,7 +532,8 @@ class B200AttnBackend(AttentionBackend):
                 with torch.cuda.stream(side):
                     ops.decode(q3[t_ext:t_end], o3[t_ext:t_end], pool.k_buffer[lid], pool.v_buffer[lid], table,
                                forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan,
-                               self.n_ctas, self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)
+                               self.n_ctas, self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype,
+                               page_size=self.page_size)
             if self.overlap_mixed != 2:
                 tail_on_side()
         if n_ext > 0 and t_ext > 0:
@@ -451,7 +541,7 @@ class B200AttnBackend(AttentionBackend):
                        forward_batch.req_pool_indices[:n_ext], forward_batch.seq_lens[:n_ext],
                        forward_batch.extend_seq_lens[:n_ext], forward_batch.extend_prefix_lens[:n_ext],
                        md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling, cap, k_scale, v_scale,
-                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window)
+                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window, page_size=self.page_size)
         if side is not None:
             if self.overlap_mixed == 2:  # prefill rows launched first, the tail fills the SMs they leave
                 tail_on_side()
@@ -463,5 +553,6 @@ class B200AttnBackend(AttentionBackend):
             #  on the extend kernel: route_decode_tail is ignored for them in init_forward_metadata)
             ops.decode(q3[t_ext:t_end], o3[t_ext:t_end], pool.k_buffer[lid], pool.v_buffer[lid], table,
                        forward_batch.req_pool_indices[n_ext:], forward_batch.seq_lens[n_ext:], self.plan, self.n_ctas,
-                       self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype)
+                       self.workspace, layer.scaling, cap, k_scale, v_scale, kv_dtype=pool.dtype,
+                       page_size=self.page_size)
         return o

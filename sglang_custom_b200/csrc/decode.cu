@@ -27,6 +27,7 @@
 #include "common.cuh"
 #include "decode_plan.cuh"
 #include "tc_ptx.cuh"
+#include "tma.cuh"
 
 namespace b200attn {
 
@@ -56,16 +57,27 @@ struct DecodeParams {
   float scale_raw;   // sm_scale * k_scale
   float logit_cap;
   float v_scale;
+  // paged-tile loads (page_size % 16 == 0): segments of a (page, K or V) box covered by one bulk-tensor copy, and the
+  // dimension order of the tensor map (0: [128 B][rows][segments], 1: [128 B][segments][rows] with one segment per copy)
+  int tma_box_segs, tma_order;
+  int page_size;  // allocator page size (b200attn_decode_paged); 1 = token-granular slots
 };
 
-constexpr int kDecodeWarps = 8;                                 // consumer warps
+struct DecodeTmaps {
+  CUtensorMap k, v;
+};
+
+constexpr int kTileWarps = 8;                                   // consumer warps that share one tile (stage)
 constexpr int kProducerThreads = 128;                           // 4 producer warps
-constexpr int kDecodeThreads = kDecodeWarps * 32 + kProducerThreads;
 constexpr int kMaxSeg = 32;
 
-template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE>
+// CW consumer warps = TG = CW / 8 tile groups of 8 warps; group g consumes the tiles t with t % TG == g, so that with
+// CW = 16 two stages of the ring are being consumed at any time (four consumer warps per SM sub-partition).
+template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE, int CW = 8, bool kTokM = false>
 struct DecodeCfg {
-  static constexpr int TS = kDecodeWarps / HB;       // token sub-tiles (warps) per head
+  static constexpr int TG = CW / kTileWarps;         // tile groups
+  static constexpr int THREADS = CW * 32 + kProducerThreads;
+  static constexpr int TS = kTileWarps / HB;         // token sub-tiles (warps) per head and tile
   static constexpr int NT = 16 * TS;                 // tokens per tile
   static constexpr int HEADB = D * KVB;              // bytes of one head row
   static constexpr int ROWB = HB * HEADB;            // bytes gathered per token (K or V)
@@ -78,14 +90,17 @@ struct DecodeCfg {
   static_assert(CHUNKS % kProducerThreads == 0, "tile must divide over the producer warps");
   static constexpr int SWZ = CPH >= 8 ? 7 : (CPH - 1);
   static constexpr int RED_ROWS = 16;
-  // cross-warp merge buffer of the TS warps of a head (dedicated: the producers refill stages asynchronously)
-  static constexpr int REDB = (TS > 1) ? (kDecodeWarps / 2) * RED_ROWS * (D + 2) * 4 : 0;
+  // cross-warp merge buffer of the TS * TG warps of a head (dedicated: the producers refill stages asynchronously).
+  // Token-major consumers (kTokM) park their whole register state lane by lane: (D/16*4 + 4) floats per lane.
+  static constexpr int RED_SLOT_F = kTokM ? (D / 16 * 4 + 4) * 32 : RED_ROWS * (D + 2);
+  static constexpr int REDB = (TS * TG > 1) ? (CW / 2) * RED_SLOT_F * 4 : 0;
   static constexpr int IDXB = 2 * NT * 4;            // double-buffered token-slot ring
   static constexpr int BARB = 2 * NSTAGE * 8;        // full[NSTAGE], empty[NSTAGE]
   static constexpr int OFF_RED = NSTAGE * STAGEB;
   static constexpr int OFF_IDX = OFF_RED + REDB;
   static constexpr int OFF_BAR = OFF_IDX + IDXB;
-  static constexpr int SMEM = OFF_BAR + BARB + 128;
+  static constexpr int SMEM = OFF_BAR + BARB + 128 + 1024;  // + slack: the stage ring starts on a 1024-byte boundary
+  static constexpr int SEGS = HEADB / 128;                  // 128-byte swizzle segments per head row (paged-tile loads)
 };
 
 struct Segment {
@@ -109,16 +124,21 @@ __device__ __forceinline__ void named_barrier(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE>
-__global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeParams p) {
-  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE, int CW, bool kTokM, bool kTma>
+__global__ void __launch_bounds__(CW * 32 + kProducerThreads, 1)
+decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM>;
   constexpr bool kFp8 = (KVB == 1);
+  constexpr int TG = Cfg::TG;
+  static_assert(!kTokM || (kFp8 && kG8), "the token-major consumer is built for FP8 K/V with a GQA group <= 8");
   constexpr bool kMmaBf16 = kQBf16 && !kFp8;  // fp8 K/V are dequantised to f16 (exact)
   constexpr int TS = Cfg::TS, NT = Cfg::NT;
   constexpr int KSTEPS = D / 16;
   constexpr int NBLK = D / 8;
 
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  // 1024-byte aligned: the 128-byte swizzle of the paged-tile (TMA) loads is keyed on shared-memory address bits 7-9
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* stage_base = smem;
   float* red_buf = reinterpret_cast<float*>(smem + Cfg::OFF_RED);
   int32_t* idx_ring = reinterpret_cast<int32_t*>(smem + Cfg::OFF_IDX);
@@ -142,19 +162,24 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
   const int32_t* first_req = plan + kPlanHeader + bs + 1;  // [n_ctas]
   const int u_begin = cta * W;
   if (u_begin >= total_units) return;  // CTA-uniform, before any barrier
+  if constexpr (kTma) {
+    // a sliding-window plan shifts the first token of a request off its page boundary: the backend keeps window layers
+    // on the row-gather instantiation, anything else is a caller bug that must not pass silently
+    if (plan[kPlanWindow] >= 0) __trap();
+  }
   const int u_end = min(u_begin + W, total_units);
 
   if (tid == 0) {
     next_req_sh = first_req[cta];
     next_unit_sh = u_begin;
     for (int s = 0; s < NSTAGE; ++s) {
-      ptx::mbar_init(full_bar(s), kProducerThreads);
-      ptx::mbar_init(empty_bar(s), kDecodeWarps);
+      ptx::mbar_init(full_bar(s), kTma ? 1 : kProducerThreads);
+      ptx::mbar_init(empty_bar(s), kTileWarps);
     }
     ptx::fence_mbar_init();
   }
   __syncthreads();
-  const bool is_producer = warp >= kDecodeWarps;
+  const bool is_producer = warp >= CW;
   int stage = 0;        // ring position of the next tile (both roles walk the same tile sequence)
   uint32_t phase = 0;
   auto advance = [&]() { if (++stage == NSTAGE) { stage = 0; phase ^= 1u; } };
@@ -163,13 +188,65 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
   // The two roles run textually separate loops (same sequence of CTA barriers) so that the register budget set by
   // setmaxnreg holds for everything a role executes.
   if (is_producer) {
-    ptx::setmaxnreg_dec<88>();
+    // (16 consumer warps: the kernel as a whole fits the 96 registers 640 threads leave -- no re-balancing.  A
+    //  setmaxnreg.inc that asks for more than the producers released blocks forever.)
+    if constexpr (CW == 8) ptx::setmaxnreg_dec<88>();
     while (true) {
       __syncthreads();  // thread 0 (a consumer) has built the next batch of segments
       const int n_segs = n_segs_sh;
       if (n_segs == 0) break;
       // ============================================================ producers
-      const int ptid = tid - kDecodeWarps * 32;
+      if constexpr (kTma) {
+        // paged-tile loads: the first producer warp alone; lane i owns page i of a tile (NT / 16 pages): one table read
+        // (the slot of the page's first row, fetched one tile ahead) and one bulk-tensor copy per box of K and of V,
+        // completion counted in bytes on the stage's `full` mbarrier.
+        if (warp == CW) {
+          constexpr int PG = NT / 16;
+          constexpr uint32_t PAGEB = 16 * Cfg::ROWB;  // bytes of a page of K (or V) for this CTA's head block
+          const int seg0 = blockIdx.y * HB * Cfg::SEGS;
+          int i_seg = 0, i_tile = 0;
+          int32_t pend = 0;
+          int pend_pages = 0;
+          auto fetch = [&]() {
+            pend_pages = 0;
+            if (i_seg >= n_segs) return;
+            const Segment& sg = segs[i_seg];
+            const int tok0 = sg.tok_begin + i_tile * NT;
+            pend_pages = min(PG, (sg.tok_end - tok0 + 15) >> 4);
+            pend = (lane < pend_pages) ? __ldg(p.req_to_token + sg.table_off + tok0 + lane * 16) : 0;
+            if (++i_tile >= seg_tiles(i_seg)) { i_tile = 0; ++i_seg; }
+          };
+          fetch();
+          for (int sg = 0; sg < n_segs; ++sg) {
+            const int ntiles = seg_tiles(sg);
+            for (int t = 0; t < ntiles; ++t) {
+              const int32_t slot = pend;
+              const int npg = pend_pages;
+              fetch();
+              ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+              const uint32_t k_s = smem_u32(stage_base + stage * Cfg::STAGEB), v_s = k_s + Cfg::TILEB;
+              if (lane == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), static_cast<uint32_t>(npg) * 2u * PAGEB);
+              __syncwarp();
+              if (lane < npg) {
+                const uint32_t dk = k_s + lane * PAGEB, dv = v_s + lane * PAGEB;
+                for (int sgm = 0; sgm < HB * Cfg::SEGS; sgm += p.tma_box_segs) {
+                  const int c1 = p.tma_order ? seg0 + sgm : slot, c2 = p.tma_order ? slot : seg0 + sgm;
+                  ptx::tma_load_3d(dk + sgm * 2048, &tm.k, 0, c1, c2, full_bar(stage));
+                  ptx::tma_load_3d(dv + sgm * 2048, &tm.v, 0, c1, c2, full_bar(stage));
+                }
+              }
+              advance();
+            }
+          }
+        } else {
+          // idle producer warps still walk the ring so that `stage` / `phase` stay in step for the next segment batch
+          for (int sg = 0; sg < n_segs; ++sg) {
+            const int ntiles = seg_tiles(sg);
+            for (int t = 0; t < ntiles; ++t) advance();
+          }
+        }
+      } else {
+      const int ptid = tid - CW * 32;
       const uint8_t* kpool = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
       const uint8_t* vpool = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(blockIdx.y) * Cfg::ROWB;
       const int64_t pool_row_bytes = p.pool_tok_stride * KVB;
@@ -223,11 +300,13 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
           advance();
         }
       }
+      }
       __syncthreads();  // the segment list may be rebuilt
     }
     asm volatile("cp.async.wait_all;\n" ::: "memory");
   } else {
-    ptx::setmaxnreg_inc<208>();
+    if constexpr (CW == 8) ptx::setmaxnreg_inc<208>();
+    int tile_no = 0;  // running tile number of this CTA (the tile groups alternate)
     while (true) {
       // ---------------- build the next batch of segments (thread 0), at most kMaxSeg
       if (tid == 0) {
@@ -257,16 +336,39 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
       const int n_segs = n_segs_sh;
       if (n_segs == 0) break;
       // ============================================================ consumers
-      const int hb = warp % HB;   // head within the CTA's head block
-      const int ts = warp / HB;   // token sub-tile
+      const int tg = warp / kTileWarps;            // tile group: consumes the tiles with tile_no % TG == tg
+      const int hb = (warp % kTileWarps) % HB;     // head within the CTA's head block
+      const int ts = (warp % kTileWarps) / HB;     // token sub-tile inside a tile
       const int qd = lane & 3;    // quad lane
       const int row = lane >> 2;  // MMA row 0..7
       const int kv_head = blockIdx.y * HB + hb;
-      auto consumer_barrier = [&]() { named_barrier(1, kDecodeWarps * 32); };
+      auto consumer_barrier = [&]() { named_barrier(1, CW * 32); };
+      // byte offset of 16-byte chunk ch of this warp's head, token tok of the tile, inside a K (or V) tile
+      auto kv_off = [&](int tok, int ch) -> uint32_t {
+        if constexpr (kTma)  // [page of the tile][segment][16 rows][128 B], swizzle keyed on the row (TMA SWIZZLE_128B)
+          return (tok >> 4) * (16 * Cfg::ROWB) + (hb * Cfg::SEGS + (ch >> 3)) * 2048 + (tok & 15) * 128 +
+                 (((ch & 7) ^ (tok & 7)) << 4);
+        else
+          return tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4);
+      };
+      // A paged-tile load brings whole pages: the rows of the last page past the end of the piece hold other tokens'
+      // (or never written) data.  K garbage is masked by select; V garbage is zeroed here so that 0 * NaN cannot
+      // reach O.  Rare (once per piece), the rows belong to this warp alone.
+      auto zero_v_tail = [&](uint32_t v_s, int nvalid) {
+        if constexpr (kTma) {
+          for (int i = lane; i < (16 - nvalid) * Cfg::CPH; i += 32) {
+            const int tok = ts * 16 + nvalid + i / Cfg::CPH;
+            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(v_s + kv_off(tok, i % Cfg::CPH)), "r"(0u) : "memory");
+          }
+          ptx::fence_proxy_async();  // the stage is refilled through the async proxy
+          __syncwarp();
+        }
+      };
       for (int sg = 0; sg < n_segs; ++sg) {
         const Segment seg = segs[sg];
         const int ntiles = (seg.tok_end - seg.tok_begin + NT - 1) / NT;
 
+        if constexpr (!kTokM) {
         // ---- Q fragments of this request (rows = q heads of the group, zero padded to 16)
         uint32_t qa[KSTEPS][4];
         {
@@ -317,13 +419,15 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
         for (int nb = 0; nb < NBLK; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
         float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
-        for (int t = 0; t < ntiles; ++t) {
+        for (int t = 0; t < ntiles; ++t, ++tile_no) {
+          if (TG > 1 && tile_no % TG != tg) { advance(); continue; }  // the other tile group's stage
           ptx::mbar_wait(full_bar(stage), phase);
           const int tok0 = seg.tok_begin + t * NT + ts * 16;  // first kv position of this warp's 16 tokens
           const int nvalid = seg.tok_end - tok0;               // <= 0: nothing to do
           const uint32_t k_s = smem_u32(stage_base + stage * Cfg::STAGEB);
           const uint32_t v_s = k_s + Cfg::TILEB;
           if (nvalid > 0) {
+          if (nvalid < 16) zero_v_tail(v_s, nvalid);
           // ---- S = Q K^T for 16 tokens (2 n-blocks of 8)
           float s[2][4];
   #pragma unroll
@@ -335,7 +439,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
               const int tok = ts * 16 + (mj >> 1) * 8 + mr;
               const int ch = 2 * ks + (mj & 1);
               uint32_t r[4];
-              ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              ldmatrix_x4(r, k_s + kv_off(tok, ch));
               mma_16816<kMmaBf16>(s[0], qa[ks], r[0], r[1]);
               mma_16816<kMmaBf16>(s[1], qa[ks], r[2], r[3]);
             }
@@ -347,7 +451,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
               const int tok = ts * 16 + (mj & 1) * 8 + mr;
               const int ch = 2 * kp + (mj >> 1);
               uint32_t r[4];
-              ldmatrix_x4(r, k_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              ldmatrix_x4(r, k_s + kv_off(tok, ch));
   #pragma unroll
               for (int half = 0; half < 2; ++half) {
                 const uint32_t r0 = r[2 * half], r1 = r[2 * half + 1];
@@ -415,7 +519,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
               const int tok = ts * 16 + (mj & 1) * 8 + mr;
               const int ch = 2 * jp + (mj >> 1);
               uint32_t r[4];
-              ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              ldmatrix_x4_trans(r, v_s + kv_off(tok, ch));
               mma_16816<kMmaBf16>(o[2 * jp], pa, r[0], r[1]);
               mma_16816<kMmaBf16>(o[2 * jp + 1], pa, r[2], r[3]);
             }
@@ -429,7 +533,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
               const int tok = ts * 16 + (mj & 1) * 8 + mr;
               const int ch = 2 * cp + (mj >> 1);
               uint32_t r[4];
-              ldmatrix_x4_trans(r, v_s + tok * Cfg::ROWB + hb * Cfg::HEADB + ((ch ^ (tok & Cfg::SWZ)) << 4));
+              ldmatrix_x4_trans(r, v_s + kv_off(tok, ch));
   #pragma unroll
               for (int half = 0; half < 2; ++half) {
                 const uint32_t lo = r[2 * half], hi = r[2 * half + 1];  // tokens 0-7, tokens 8-15
@@ -455,15 +559,16 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
           l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
           l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
         }
-        if constexpr (TS > 1) {
+        if constexpr (TS * TG > 1) {
           // tree merge: in each round the upper half of the token sub-tiles hands its state to the lower half
           constexpr int RSTRIDE = D + 2;
-                  float* red = red_buf;  // dedicated: the producers refill stages asynchronously
+          float* red = red_buf;  // dedicated: the producers refill stages asynchronously
+          const int tsa = tg * TS + ts;  // this warp's place among the TS * TG partial states of the head
   #pragma unroll
-          for (int half = TS / 2; half >= 1; half >>= 1) {
+          for (int half = TS * TG / 2; half >= 1; half >>= 1) {
             consumer_barrier();
-            if (ts >= half && ts < 2 * half) {
-              float* dst = red + ((ts - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+            if (tsa >= half && tsa < 2 * half) {
+              float* dst = red + ((tsa - half) * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
   #pragma unroll
               for (int nb = 0; nb < NBLK; ++nb) {
                 *reinterpret_cast<float2*>(dst + row * RSTRIDE + nb * 8 + 2 * qd) = make_float2(o[nb][0], o[nb][1]);
@@ -476,8 +581,8 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
               }
             }
             consumer_barrier();
-            if (ts < half) {
-              const float* src = red + (ts * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
+            if (tsa < half) {
+              const float* src = red + (tsa * HB + hb) * Cfg::RED_ROWS * RSTRIDE;
               {
                 const float2 ml = *reinterpret_cast<const float2*>(src + row * RSTRIDE + D);
                 const float mn = fmaxf(m0, ml.x);
@@ -508,7 +613,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
           }
         }
 
-        if (ts == 0) {
+        if (ts == 0 && tg == 0) {
   #pragma unroll
           for (int rr = 0; rr < (kG8 ? 1 : 2); ++rr) {
             const int r = row + rr * 8;
@@ -551,6 +656,203 @@ __global__ void __launch_bounds__(kDecodeThreads, 1) decode_kernel(const DecodeP
                                   o[2 * c][2 * rr + 1] * inv, o[2 * c + 1][2 * rr + 1] * inv);
               }
               if (qd == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
+            }
+          }
+        }
+        } else {
+          // ================================================================ token-major consumer (FP8 K/V, G <= 8)
+          // The 16 tokens of the warp are the M dimension of mma.sync.m16n8k16 and the (up to 8) q heads of the GQA
+          // group its N dimension: S^T = K Q^T and O^T = V^T P^T.  Against the head-major form above (heads padded
+          // to 16 MMA rows) this halves the MMA count and the accumulator registers, which is what lets 16 consumer
+          // warps fit -- the FP8 stream needs the extra warps because every byte pays an e4m3 -> f16 conversion
+          // (F2FP) in front of the MMA and the chain LDSM -> F2FP -> HMMA -> softmax -> HMMA of one warp is long.
+          // Thread (r = lane / 4, qd): S^T rows r, r + 8 (tokens), columns 2qd, 2qd + 1 (heads).
+          constexpr int NB = D / 16;  // accumulator blocks: even cp -> "even d" rows, odd -> "odd d" rows (see PV)
+          uint32_t qb[KSTEPS][2];
+          {
+            const uint16_t* qbase = reinterpret_cast<const uint16_t*>(p.q) + seg.batch * p.q_tok_stride;
+            const int Gr = p.Gr;
+            const uint16_t* qrow = qbase + (row / Gr) * p.q_sub_stride + static_cast<int64_t>(kv_head * Gr + row % Gr) * D;
+            const bool vq = row < G;
+  #pragma unroll
+            for (int ks = 0; ks < KSTEPS; ++ks) {
+              // a K register of ldmatrix holds d = 16*ks' + 4*qd + {0,1,2,3} (bytes); the contraction index is
+              // permuted identically here: b0 = d 4qd + {0,1}, b1 = d 4qd + {2,3}
+              uint2 t = make_uint2(0u, 0u);
+              if (vq) t = *reinterpret_cast<const uint2*>(qrow + ks * 16 + 4 * qd);
+              if constexpr (kQBf16) { t.x = ptx::bf16x2_to_f16x2(t.x); t.y = ptx::bf16x2_to_f16x2(t.y); }
+              qb[ks][0] = t.x; qb[ks][1] = t.y;
+            }
+          }
+          float o[NB][4];
+  #pragma unroll
+          for (int nb = 0; nb < NB; ++nb) { o[nb][0] = o[nb][1] = o[nb][2] = o[nb][3] = 0.f; }
+          float mh0 = -INFINITY, mh1 = -INFINITY;  // running maxima of heads 2qd, 2qd + 1 (log2 domain, scaled)
+          float lh0 = 0.f, lh1 = 0.f;              // this thread's share of the row sums (reduced at the end)
+          const int mj = lane >> 3, mr = lane & 7;
+
+          for (int t = 0; t < ntiles; ++t, ++tile_no) {
+            if (TG > 1 && tile_no % TG != tg) { advance(); continue; }  // the other tile group's stage
+            ptx::mbar_wait(full_bar(stage), phase);
+            const int tok0 = seg.tok_begin + t * NT + ts * 16;
+            const int nvalid = seg.tok_end - tok0;
+            const uint32_t k_s = smem_u32(stage_base + stage * Cfg::STAGEB);
+            const uint32_t v_s = k_s + Cfg::TILEB;
+            if (nvalid > 0) {
+              if (nvalid < 16) zero_v_tail(v_s, nvalid);
+              // ---- S^T = K Q^T: A = K (16 tokens x 16 d per step, dequantised), B = Q^T from registers
+              float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};  // two chains (even / odd k-steps)
+  #pragma unroll
+              for (int kp = 0; kp < KSTEPS / 2; ++kp) {
+                const int tok = ts * 16 + (mj & 1) * 8 + mr;
+                const int ch = 2 * kp + (mj >> 1);
+                uint32_t r[4];  // (tok 0-7, ch), (tok 8-15, ch), (tok 0-7, ch + 1), (tok 8-15, ch + 1)
+                ldmatrix_x4(r, k_s + kv_off(tok, ch));
+                uint32_t a[4];
+                a[0] = e4m3x2_to_f16x2(r[0] & 0xffff); a[2] = e4m3x2_to_f16x2(r[0] >> 16);
+                a[1] = e4m3x2_to_f16x2(r[1] & 0xffff); a[3] = e4m3x2_to_f16x2(r[1] >> 16);
+                mma_16816<false>(sa, a, qb[2 * kp][0], qb[2 * kp][1]);
+                a[0] = e4m3x2_to_f16x2(r[2] & 0xffff); a[2] = e4m3x2_to_f16x2(r[2] >> 16);
+                a[1] = e4m3x2_to_f16x2(r[3] & 0xffff); a[3] = e4m3x2_to_f16x2(r[3] >> 16);
+                mma_16816<false>(sb, a, qb[2 * kp + 1][0], qb[2 * kp + 1][1]);
+              }
+              float x0 = sa[0] + sb[0], x1 = sa[1] + sb[1], x2 = sa[2] + sb[2], x3 = sa[3] + sb[3];
+              if (p.logit_cap > 0.f) {
+                const float c = p.scale_raw / p.logit_cap, d = p.logit_cap * kLog2e;
+                x0 = d * fast_tanh(x0 * c); x1 = d * fast_tanh(x1 * c);
+                x2 = d * fast_tanh(x2 * c); x3 = d * fast_tanh(x3 * c);
+              } else {
+                x0 *= p.scale_log2; x1 *= p.scale_log2; x2 *= p.scale_log2; x3 *= p.scale_log2;
+              }
+              if (nvalid < 16) {  // ragged end of the piece (warp-uniform)
+                if (row >= nvalid) { x0 = -INFINITY; x1 = -INFINITY; }
+                if (row + 8 >= nvalid) { x2 = -INFINITY; x3 = -INFINITY; }
+              }
+              // ---- online softmax per head: the maximum runs over the token rows (lane bits 2..4)
+              float mx0 = fmaxf(x0, x2), mx1 = fmaxf(x1, x3);
+  #pragma unroll
+              for (int sh = 4; sh <= 16; sh <<= 1) {
+                mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, sh));
+                mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, sh));
+              }
+              const float mn0 = fmaxf(mh0, mx0), mn1 = fmaxf(mh1, mx1);  // finite: token tok0 is valid
+              const bool grew = (mn0 > mh0) || (mn1 > mh1);
+              if (__any_sync(0xffffffffu, grew)) {  // lazy rescale: a running maximum rarely moves after the first tiles
+                const float al0 = fast_exp2(mh0 - mn0), al1 = fast_exp2(mh1 - mn1);
+                lh0 *= al0; lh1 *= al1;
+  #pragma unroll
+                for (int nb = 0; nb < NB; ++nb) { o[nb][0] *= al0; o[nb][1] *= al1; o[nb][2] *= al0; o[nb][3] *= al1; }
+                mh0 = mn0; mh1 = mn1;
+              }
+              const float p0 = fast_exp2(x0 - mh0), p1 = fast_exp2(x1 - mh1);
+              const float p2 = fast_exp2(x2 - mh0), p3 = fast_exp2(x3 - mh1);
+              lh0 += p0 + p2; lh1 += p1 + p3;
+              // P^T as the B operand: transpose the two 8x8 (token x head) blocks across the warp
+              uint32_t b0 = pack2<false>(p0, p1), b1 = pack2<false>(p2, p3);
+              asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;\n" : "=r"(b0) : "r"(b0));
+              asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;\n" : "=r"(b1) : "r"(b1));
+              // ---- O^T += V^T P^T: a transposed b16 ldmatrix of fp8 rows hands a thread (tok 2qd: d0 d1), (tok 2qd+1:
+              // d0 d1) with d0 = 16*ch + 2*r; one byte permute groups them per d, and the "even d" / "odd d" halves
+              // feed two MMAs whose rows are d = 32cp + 2r (+16 for rows 8-15) resp. + 1.
+  #pragma unroll
+              for (int cp = 0; cp < D / 32; ++cp) {
+                const int tok = ts * 16 + (mj >> 1) * 8 + mr;
+                const int ch = 2 * cp + (mj & 1);
+                uint32_t r[4];  // (tok 0-7, ch), (tok 0-7, ch + 1), (tok 8-15, ch), (tok 8-15, ch + 1)
+                ldmatrix_x4_trans(r, v_s + kv_off(tok, ch));
+                uint32_t ae[4], ao[4];
+  #pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const uint32_t g = __byte_perm(r[i], 0, 0x3120);  // (t0 d0, t1 d0, t0 d1, t1 d1)
+                  ae[i] = e4m3x2_to_f16x2(g & 0xffff);
+                  ao[i] = e4m3x2_to_f16x2(g >> 16);
+                }
+                mma_16816<false>(o[2 * cp], ae, b0, b1);
+                mma_16816<false>(o[2 * cp + 1], ao, b0, b1);
+              }
+            }
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(empty_bar(stage));
+            advance();
+          }  // tiles
+
+          // ---- finish the piece: merge the TS * TG warps of a head (whole register state, lane by lane), store
+          if constexpr (TS * TG > 1) {
+            const int tsa = tg * TS + ts;
+            constexpr int SLOT = Cfg::RED_SLOT_F;
+  #pragma unroll
+            for (int half = TS * TG / 2; half >= 1; half >>= 1) {
+              consumer_barrier();
+              if (tsa >= half && tsa < 2 * half) {
+                float* dst = red_buf + ((tsa - half) * HB + hb) * SLOT + lane;
+  #pragma unroll
+                for (int nb = 0; nb < NB; ++nb) {
+  #pragma unroll
+                  for (int e = 0; e < 4; ++e) dst[(nb * 4 + e) * 32] = o[nb][e];
+                }
+                dst[(NB * 4 + 0) * 32] = mh0; dst[(NB * 4 + 1) * 32] = mh1;
+                dst[(NB * 4 + 2) * 32] = lh0; dst[(NB * 4 + 3) * 32] = lh1;
+              }
+              consumer_barrier();
+              if (tsa < half) {
+                const float* src = red_buf + (tsa * HB + hb) * SLOT + lane;
+                const float om0 = src[(NB * 4 + 0) * 32], om1 = src[(NB * 4 + 1) * 32];
+                const float mn0 = fmaxf(mh0, om0), mn1 = fmaxf(mh1, om1);
+                const float a0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(mh0 - mn0);
+                const float c0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(om0 - mn0);
+                const float a1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(mh1 - mn1);
+                const float c1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(om1 - mn1);
+                mh0 = mn0; mh1 = mn1;
+                lh0 = lh0 * a0 + src[(NB * 4 + 2) * 32] * c0;
+                lh1 = lh1 * a1 + src[(NB * 4 + 3) * 32] * c1;
+  #pragma unroll
+                for (int nb = 0; nb < NB; ++nb) {
+                  o[nb][0] = o[nb][0] * a0 + src[(nb * 4 + 0) * 32] * c0;
+                  o[nb][1] = o[nb][1] * a1 + src[(nb * 4 + 1) * 32] * c1;
+                  o[nb][2] = o[nb][2] * a0 + src[(nb * 4 + 2) * 32] * c0;
+                  o[nb][3] = o[nb][3] * a1 + src[(nb * 4 + 3) * 32] * c1;
+                }
+              }
+            }
+          }
+          if (ts == 0 && tg == 0) {
+  #pragma unroll
+            for (int sh = 4; sh <= 16; sh <<= 1) {
+              lh0 += __shfl_xor_sync(0xffffffffu, lh0, sh);
+              lh1 += __shfl_xor_sync(0xffffffffu, lh1, sh);
+            }
+  #pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              const int r = 2 * qd + hh;  // virtual head (row of the GQA group)
+              if (r >= G) continue;
+              const float m = hh ? mh1 : mh0, l = hh ? lh1 : lh0;
+              const float inv = (l > 0.f) ? p.v_scale / l : 0.f;
+              const float lse = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+              const int head = kv_head * G + r;
+              const int sub = r / p.Gr, head_real = kv_head * p.Gr + r % p.Gr;
+              // this thread holds d = 32cp + 2*row + {0 (block 2cp), 1 (block 2cp+1)} and the same + 16
+              if (seg.slot < 0) {
+                uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + seg.batch * p.out_tok_stride +
+                                sub * p.out_sub_stride + static_cast<int64_t>(head_real) * D + 2 * row;
+  #pragma unroll
+                for (int cp = 0; cp < D / 32; ++cp) {
+                  *reinterpret_cast<uint32_t*>(dst + 32 * cp) =
+                      pack2<kQBf16>(o[2 * cp][hh] * inv, o[2 * cp + 1][hh] * inv);
+                  *reinterpret_cast<uint32_t*>(dst + 32 * cp + 16) =
+                      pack2<kQBf16>(o[2 * cp][2 + hh] * inv, o[2 * cp + 1][2 + hh] * inv);
+                }
+                if (p.lse_out != nullptr && row == 0)
+                  p.lse_out[static_cast<int64_t>(seg.batch) * p.lse_req_stride + sub * p.Hq_real + head_real] = lse;
+              } else {
+                float* dst = p.ws_o + (static_cast<int64_t>(seg.slot) * p.Hq + head) * D + 2 * row;
+  #pragma unroll
+                for (int cp = 0; cp < D / 32; ++cp) {
+                  *reinterpret_cast<float2*>(dst + 32 * cp) = make_float2(o[2 * cp][hh] * inv, o[2 * cp + 1][hh] * inv);
+                  *reinterpret_cast<float2*>(dst + 32 * cp + 16) =
+                      make_float2(o[2 * cp][2 + hh] * inv, o[2 * cp + 1][2 + hh] * inv);
+                }
+                if (row == 0) p.ws_lse[static_cast<int64_t>(seg.slot) * p.Hq + head] = lse;
+              }
             }
           }
         }
@@ -696,23 +998,107 @@ __global__ void __launch_bounds__(kMergeWarps * 32) decode_merge_kernel(const De
   }
 }
 
-template <int D, int HB, int KVB, bool kQBf16, bool kG8>
-static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
-  constexpr int kWant = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+// stage count: as many stages as fit next to the merge buffer (at least 2, at most 6; 3 are enough for 64 KiB stages)
+template <int D, int HB, int KVB, int CW, bool kTokM>
+constexpr int decode_stages() {
   constexpr int kStatic = 2048;
-  constexpr int NSTAGE = (DecodeCfg<D, HB, KVB, kWant>::SMEM + kStatic <= 227 * 1024) ? kWant : kWant - 1;
-  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE>;
+  int n = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+  while (n > 2) {
+    const int stageb = 2 * (16 * (kTileWarps / HB)) * HB * D * KVB;
+    const int tstg = (kTileWarps / HB) * (CW / kTileWarps);
+    const int slot_f = kTokM ? (D / 16 * 4 + 4) * 32 : 16 * (D + 2);
+    const int redb = tstg > 1 ? (CW / 2) * slot_f * 4 : 0;
+    const int total = n * stageb + redb + 2 * 16 * (kTileWarps / HB) * 4 + 2 * n * 8 + 128 + 1024;
+    if (total + kStatic <= 227 * 1024) break;
+    --n;
+  }
+  return n;
+}
+
+// B200ATTN_DECODE_TMA=0 keeps page_size >= 16 pools on the row-gather producers (for A/B timing; default 1)
+static bool decode_tma_enabled() {
+  static const bool on = [] { const char* e = getenv("B200ATTN_DECODE_TMA"); return e ? atoi(e) != 0 : true; }();
+  return on;
+}
+
+// Tensor maps of the K and V pools for the paged-tile producers.  Encoding is host-only work (about a microsecond);
+// the last few (pool, geometry) pairs are cached per thread -- a decode step walks the same layers every time.
+struct TmapKey {
+  const void* k; const void* v; int64_t row_bytes; int kvb, row_segs, box_segs;
+  bool operator==(const TmapKey& o) const {
+    return k == o.k && v == o.v && row_bytes == o.row_bytes && kvb == o.kvb && row_segs == o.row_segs && box_segs == o.box_segs;
+  }
+};
+static int decode_tmaps(const DecodeParams& p, int kvb, int D, int HB, const DecodeTmaps** out, int* box_segs_out) {
+  constexpr int kSlots = 256;
+  struct Entry { TmapKey key; DecodeTmaps maps; bool used; };
+  static thread_local Entry cache[kSlots];
+  const int row_segs = p.Hkv * D * kvb / 128;
+  const int box_segs = HB * D * kvb / 128;
+  const TmapKey key{p.k_pool, p.v_pool, p.pool_tok_stride * kvb, kvb, row_segs, box_segs};
+  const size_t h = (reinterpret_cast<uintptr_t>(p.k_pool) >> 8) * 0x9E3779B97F4A7C15ull;
+  Entry& e = cache[(h >> 40) % kSlots];
+  if (!e.used || !(e.key == key)) {
+    int rc = encode_pool_tmap(&e.maps.k, p.k_pool, kvb, key.row_bytes, row_segs, 16, box_segs);
+    if (rc != B200ATTN_OK) return rc;
+    rc = encode_pool_tmap(&e.maps.v, p.v_pool, kvb, key.row_bytes, row_segs, 16, box_segs);
+    if (rc != B200ATTN_OK) return rc;
+    e.key = key;
+    e.used = true;
+  }
+  *out = &e.maps;
+  *box_segs_out = box_segs;
+  return B200ATTN_OK;
+}
+
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, int CW, bool kTokM, bool kTma>
+static int launch_decode_cw(const DecodeParams& p_in, int head_groups, cudaStream_t st) {
+  constexpr int kStatic = 2048;
+  constexpr int NSTAGE = decode_stages<D, HB, KVB, CW, kTokM>();
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM>;
   static_assert(Cfg::SMEM + kStatic <= 227 * 1024, "decode staging exceeds the shared memory of one CTA");
-  auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE>;
+  DecodeParams p = p_in;
+  static const DecodeTmaps no_maps{};
+  const DecodeTmaps* maps = &no_maps;
+  if constexpr (kTma) {
+    const int rc = decode_tmaps(p, KVB, D, HB, &maps, &p.tma_box_segs);
+    if (rc != B200ATTN_OK) return rc;
+    p.tma_order = 0;
+  }
+  auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE, CW, kTokM, kTma>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
     configured = true;
   }
   dim3 grid(p.n_ctas, head_groups, 1);
-  kern<<<grid, kDecodeThreads, Cfg::SMEM, st>>>(p);
+  kern<<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(p, *maps);
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
+}
+
+// B200ATTN_DECODE_FP8_TOKM=0 keeps FP8 pools on the head-major 8-warp consumer (for A/B timing; default 1)
+static bool fp8_tokm_enabled() {
+  static const bool on = [] { const char* e = getenv("B200ATTN_DECODE_FP8_TOKM"); return e ? atoi(e) != 0 : true; }();
+  return on;
+}
+
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, bool kTma>
+static int launch_decode_t(const DecodeParams& p, int head_groups, cudaStream_t st) {
+  if constexpr (KVB == 1 && kG8) {
+    if (fp8_tokm_enabled()) return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma>(p, head_groups, st);
+  }
+  return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 8, false, kTma>(p, head_groups, st);
+}
+
+template <int D, int HB, int KVB, bool kQBf16, bool kG8>
+static int launch_decode(const DecodeParams& p, int head_groups, cudaStream_t st) {
+  // paged-tile loads: D = 128 (head rows of 128 or 256 bytes = whole swizzle segments), pages of a multiple of 16
+  if constexpr (D == 128) {
+    if (p.page_size >= 16 && p.page_size % 16 == 0 && decode_tma_enabled())
+      return launch_decode_t<D, HB, KVB, kQBf16, kG8, true>(p, head_groups, st);
+  }
+  return launch_decode_t<D, HB, KVB, kQBf16, kG8, false>(p, head_groups, st);
 }
 
 template <int D, int KVB, bool kQBf16, bool kG8>
@@ -787,6 +1173,7 @@ static int decode_setup(DecodeParams& p, const void* q, int64_t q_tok_stride, vo
   p.scale_log2 = sm_scale * k_scale * kLog2e;
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
+  p.tma_box_segs = 1; p.tma_order = 0; p.page_size = 1;
   return B200ATTN_OK;
 }
 
@@ -821,39 +1208,42 @@ static int launch_merge(const DecodeParams& p, int D, bool q_bf16, cudaStream_t 
       req_pool_indices, seq_lens, idx_is_i64, bs, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap, k_scale,    \
       v_scale, plan, n_ctas, workspace, workspace_bytes, lse_out
 
-extern "C" B2_EXPORT int b200attn_decode(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
-                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
-                               const int32_t* req_to_token, int64_t table_stride,
-                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
-                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
-                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
-                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
-                               b200attn_stream_t stream) {
+#define B2_DECODE_PARAMS                                                                                          \
+  const void *q, int64_t q_tok_stride, void *out, int64_t out_tok_stride, const void *k_pool, const void *v_pool, \
+      int64_t pool_tok_stride, const int32_t *req_to_token, int64_t table_stride, const void *req_pool_indices,  \
+      const void *seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,           \
+      float sm_scale, float logit_cap, float k_scale, float v_scale, const int32_t *plan, int n_ctas,            \
+      void *workspace, size_t workspace_bytes, float *lse_out
+
+static int decode_entry(B2_DECODE_PARAMS, int page_size, bool merge, b200attn_stream_t stream) {
   if (bs == 0) return B200ATTN_OK;
+  B2_REQUIRE(page_size >= 1, B200ATTN_ERR_INVALID, "decode: page_size=%d", page_size);
   DecodeParams p;
   const int rc = decode_setup(p, B2_DECODE_ARGS, true);
   if (rc != B200ATTN_OK) return rc;
+  p.page_size = page_size;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool q_bf16 = q_dtype == B200ATTN_BF16;
   const int rc2 = launch_partial(p, D, elem_size(kv_dtype), q_bf16, st);
-  if (rc2 != B200ATTN_OK) return rc2;
+  if (rc2 != B200ATTN_OK || !merge) return rc2;
   return launch_merge(p, D, q_bf16, st);
 }
 
+extern "C" B2_EXPORT int b200attn_decode(B2_DECODE_PARAMS, b200attn_stream_t stream) {
+  return decode_entry(B2_DECODE_ARGS, 1, true, stream);
+}
+
 // stage 1 only: the persistent split-KV kernel (final outputs of unsplit requests + fp32 partials)
-extern "C" B2_EXPORT int b200attn_decode_partial(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
-                               const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
-                               const int32_t* req_to_token, int64_t table_stride,
-                               const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs,
-                               int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
-                               float logit_cap, float k_scale, float v_scale, const int32_t* plan,
-                               int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
-                               b200attn_stream_t stream) {
-  if (bs == 0) return B200ATTN_OK;
-  DecodeParams p;
-  const int rc = decode_setup(p, B2_DECODE_ARGS, true);
-  if (rc != B200ATTN_OK) return rc;
-  return launch_partial(p, D, elem_size(kv_dtype), q_dtype == B200ATTN_BF16, static_cast<cudaStream_t>(stream));
+extern "C" B2_EXPORT int b200attn_decode_partial(B2_DECODE_PARAMS, b200attn_stream_t stream) {
+  return decode_entry(B2_DECODE_ARGS, 1, false, stream);
+}
+
+// b200attn_decode (stage = 0) / b200attn_decode_partial (stage = 1) for a pool whose allocator hands out pages of
+// page_size consecutive slots: with page_size % 16 == 0 and D = 128 the producers read one table entry per 16-token
+// unit and fetch the unit's K and V rows as bulk-tensor (TMA) boxes.
+extern "C" B2_EXPORT int b200attn_decode_paged(B2_DECODE_PARAMS, int page_size, int stage, b200attn_stream_t stream) {
+  B2_REQUIRE(stage == 0 || stage == 1, B200ATTN_ERR_INVALID, "decode_paged: stage=%d", stage);
+  return decode_entry(B2_DECODE_ARGS, page_size, stage == 0, stream);
 }
 
 // stage 2 only: LSE merge of the partials of requests that were cut across CTAs
@@ -873,7 +1263,7 @@ extern "C" B2_EXPORT int b200attn_decode_merge(void* out, int64_t out_tok_stride
 // speculative-decoding verify batch (TARGET_VERIFY, triton_backend.py:227-264), where every draft token sees the whole
 // prefix.  The nq * G rows of a kv head ride the MMA row dimension the GQA group already uses, so K/V are streamed from
 // HBM once for all of them (nq * Hq / Hkv <= 16).  The caller merges the draft-token part with b200attn_merge_state.
-extern "C" B2_EXPORT int b200attn_decode_multiq(
+static int decode_multiq_entry(int page_size,
     const void* q, int64_t q_req_stride, int64_t q_tok_stride, void* out, int64_t out_req_stride, int64_t out_tok_stride,
     const void* k_pool, const void* v_pool, int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride,
     const void* req_pool_indices, const void* seq_lens, int idx_is_i64, int bs, int nq, int Hq, int Hkv, int D,
@@ -881,6 +1271,7 @@ extern "C" B2_EXPORT int b200attn_decode_multiq(
     int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out, int64_t lse_req_stride,
     b200attn_stream_t stream) {
   if (bs == 0 || nq == 0) return B200ATTN_OK;
+  B2_REQUIRE(page_size >= 1, B200ATTN_ERR_INVALID, "decode_multiq: page_size=%d", page_size);
   B2_REQUIRE(nq > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && nq * (Hq / Hkv) <= 16, B200ATTN_ERR_UNSUPPORTED,
              "decode_multiq: nq * Hq / Hkv = %d * %d / %d must be <= 16", nq, Hq, Hkv);
   B2_REQUIRE(q_tok_stride % 8 == 0 && out_tok_stride % 8 == 0, B200ATTN_ERR_INVALID,
@@ -894,9 +1285,31 @@ extern "C" B2_EXPORT int b200attn_decode_multiq(
   p.Gr = Hq / Hkv; p.Hq_real = Hq;
   p.q_sub_stride = q_tok_stride; p.out_sub_stride = out_tok_stride;
   p.lse_req_stride = lse_req_stride;
+  p.page_size = page_size;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool q_bf16 = q_dtype == B200ATTN_BF16;
   const int rc2 = launch_partial(p, D, elem_size(kv_dtype), q_bf16, st);
   if (rc2 != B200ATTN_OK) return rc2;
   return launch_merge(p, D, q_bf16, st);
+}
+
+#define B2_MULTIQ_PARAMS                                                                                         \
+  const void *q, int64_t q_req_stride, int64_t q_tok_stride, void *out, int64_t out_req_stride,                 \
+      int64_t out_tok_stride, const void *k_pool, const void *v_pool, int64_t pool_tok_stride,                  \
+      const int32_t *req_to_token, int64_t table_stride, const void *req_pool_indices, const void *seq_lens,    \
+      int idx_is_i64, int bs, int nq, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,        \
+      float logit_cap, float k_scale, float v_scale, const int32_t *plan, int n_ctas, void *workspace,          \
+      size_t workspace_bytes, float *lse_out, int64_t lse_req_stride
+#define B2_MULTIQ_ARGS                                                                                           \
+  q, q_req_stride, q_tok_stride, out, out_req_stride, out_tok_stride, k_pool, v_pool, pool_tok_stride,          \
+      req_to_token, table_stride, req_pool_indices, seq_lens, idx_is_i64, bs, nq, Hq, Hkv, D, q_dtype, kv_dtype, \
+      sm_scale, logit_cap, k_scale, v_scale, plan, n_ctas, workspace, workspace_bytes, lse_out, lse_req_stride
+
+extern "C" B2_EXPORT int b200attn_decode_multiq(B2_MULTIQ_PARAMS, b200attn_stream_t stream) {
+  return decode_multiq_entry(1, B2_MULTIQ_ARGS, stream);
+}
+
+// b200attn_decode_multiq for a paged pool (see b200attn_decode_paged)
+extern "C" B2_EXPORT int b200attn_decode_multiq_paged(B2_MULTIQ_PARAMS, int page_size, b200attn_stream_t stream) {
+  return decode_multiq_entry(page_size, B2_MULTIQ_ARGS, stream);
 }

@@ -19,7 +19,8 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
                        const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D,
                        int q_dtype, int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
                        int causal, int impl, float* lse_out, int window, const uint8_t* custom_mask,
-                       const int64_t* mask_indptr, int skip_prefix_mask, b200attn_stream_t stream) {
+                       const int64_t* mask_indptr, int skip_prefix_mask, int page_size, b200attn_stream_t stream) {
+  B2_REQUIRE(page_size >= 1, B200ATTN_ERR_INVALID, "extend: page_size=%d", page_size);
   B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0 && max_extend_len >= 0, B200ATTN_ERR_INVALID,
              "extend: bad sizes bs=%d Hq=%d Hkv=%d max_extend_len=%d", bs, Hq, Hkv, max_extend_len);
   if (bs == 0 || max_extend_len == 0) return B200ATTN_OK;
@@ -56,6 +57,7 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
   p.logit_cap = logit_cap;
   p.v_scale = v_scale;
   p.window = window; p.custom_mask = custom_mask; p.mask_indptr = mask_indptr; p.skip_prefix_mask = skip_prefix_mask;
+  p.page_size = page_size;
   {
     // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
     static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 0; }();
@@ -111,7 +113,7 @@ extern "C" B2_EXPORT int b200attn_extend(const void* q, int64_t q_tok_stride, vo
   return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
                      table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
                      extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
-                     k_scale, v_scale, causal, impl, lse_out, -1, nullptr, nullptr, 1, stream);
+                     k_scale, v_scale, causal, impl, lse_out, -1, nullptr, nullptr, 1, 1, stream);
 }
 
 // Sliding-window layers and speculative-decoding verify batches: TritonAttnBackend.forward_extend with
@@ -131,5 +133,24 @@ extern "C" B2_EXPORT int b200attn_extend_masked(
                      table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
                      extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
                      k_scale, v_scale, causal, impl, lse_out, sliding_window_size, custom_mask,
-                     mask_indptr, skip_prefix_custom_mask, stream);
+                     mask_indptr, skip_prefix_custom_mask, 1, stream);
+}
+
+// b200attn_extend_masked for a paged pool (slot layout of mem_cache/allocator.py:444-447, see b200attn_decode_paged):
+// with page_size % 16 == 0 and a 16-bit pool the tcgen05 kernel's K/V tiles arrive as bulk-tensor (TMA) boxes.
+extern "C" B2_EXPORT int b200attn_extend_paged(
+    const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool, const void* v_pool,
+    int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+    const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+    const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,
+    float sm_scale, float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
+    const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask, float* lse_out,
+    int page_size, b200attn_stream_t stream) {
+  B2_REQUIRE(sliding_window_size >= B200ATTN_WINDOW_NEW_TOKENS_ONLY, B200ATTN_ERR_INVALID,
+             "extend_paged: sliding_window_size=%d", sliding_window_size);
+  return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
+                     table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
+                     extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, logit_cap,
+                     k_scale, v_scale, causal, impl, lse_out, sliding_window_size, custom_mask,
+                     mask_indptr, skip_prefix_custom_mask, page_size, stream);
 }

@@ -37,6 +37,7 @@ struct ExtendParams {
   const uint8_t* custom_mask;
   const int64_t* mask_indptr;
   int skip_prefix_mask;
+  int page_size;  // allocator page size (b200attn_extend_paged); % 16 == 0 with a 16-bit pool: bulk-tensor (TMA) K/V loads
   int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 0: measured best at C3)
 };
 

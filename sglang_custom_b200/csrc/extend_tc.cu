@@ -37,6 +37,7 @@
 //     stream the K/V of one request, which therefore stays in L2 across its 16 head pairs x q tiles.
 #include "extend.cuh"
 #include "tc_ptx.cuh"
+#include "tma.cuh"
 
 namespace b200attn {
 namespace tc {
@@ -184,10 +185,18 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 // the MMA runs in f16 (bf16 model over an FP8 KV cache): Q is converted on its way into shared memory.
 // kWin: sliding-window layers (p.window >= 0, semantics in extend.cuh): the K/V walk starts at the 128-key tile that
 // holds the first prefix key inside the window, and the first tiles carry a per-row lower bound.
-template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false, bool kWin = false>
+struct ExtendTmaps {
+  CUtensorMap k, v;
+};
+
+// kTma: paged-tile loads (page_size % 16 == 0, 16-bit pools): one producer warp reads one table entry per 16-key page
+// and fetches the page's K (V) rows of this kv head as two bulk-tensor boxes of 16 rows x 128 B -- the 128-byte
+// swizzle of the copy IS the UMMA canonical layout the row gathers build by hand.
+template <bool kBf16, int kEmu, bool kProf, bool kFp8 = false, bool kQCvt = false, bool kWin = false, bool kTma = false>
 __global__ void __launch_bounds__(kThreads, 1)
-extend_tc_kernel(const ExtendParams p, const int pair_heads) {
+extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_constant__ ExtendTmaps tm) {
   static_assert(!(kFp8 && kBf16) && !(kQCvt && kBf16), "FP8 KV runs the MMA in f16");
+  static_assert(!(kTma && kFp8), "FP8 pools are expanded in registers: no bulk-tensor path");
   constexpr bool kOutBf16 = kBf16 || kQCvt;  // dtype of q and out in global memory
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms repeat every 1024 B
@@ -236,9 +245,9 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
   if (tid == 0) {
     ptx::mbar_init(bar(Q_FULL), 256);
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(bar(K_FULL + i), kProducerWarps * 32);
+      ptx::mbar_init(bar(K_FULL + i), kTma ? 1 : kProducerWarps * 32);
       ptx::mbar_init(bar(K_EMPTY + i), 1);
-      ptx::mbar_init(bar(V_FULL + i), kProducerWarps * 32);
+      ptx::mbar_init(bar(V_FULL + i), kTma ? 1 : kProducerWarps * 32);
       ptx::mbar_init(bar(V_EMPTY + i), 1);
       ptx::mbar_init(bar(S_FULL + i), 1);
       ptx::mbar_init(bar(O_FULL + i), 1);
@@ -483,7 +492,61 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads) {
         sreg[c] = (m < 16 && tok < kv_len) ? __ldg(trow + tok) : 0;  // past the end: the dummy slot (masked later)
       }
     };
-    if constexpr (!kFp8) {
+    if constexpr (kTma) {
+      if (pw == 0) {
+        const int64_t row_bytes = p.pool_tok_stride * 2;
+        const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2);
+        const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2);
+        const int seg0 = 2 * kv_head;  // a 256-byte head row = two 128-byte segments of the pool row
+        // lane i < 8 owns page i of a tile: the slot of its first row, fetched one tile ahead
+        auto page_slot = [&](int j) {
+          const int tok = kv_base + j * kTile + 16 * lane;
+          return (lane < 8 && tok < kv_len) ? __ldg(trow + tok) : 0;
+        };
+        // Pages that lie completely below kv_len arrive as boxes.  The rest of the tile (the ragged last page and
+        // everything behind it -- only the last tile of a CTA has any) is written through the generic proxy: real rows
+        // copied, rows past kv_len zeroed, so that neither another request's rows nor stale shared memory (0 * NaN)
+        // can reach O.  One arrival covers both: the stores are fenced before expect_tx.
+        auto load_tile = [&](const CUtensorMap* map, const uint8_t* base, uint32_t tile, uint32_t full, int slot, int j) {
+          const int tok0 = kv_base + j * kTile;
+          const int nvalid = min(kTile, kv_len - tok0);
+          const int n_full = nvalid >> 4;
+          if (n_full < 8) {
+            for (int i = n_full * 256 + lane; i < kTile * 16; i += 32) {
+              const int r = i >> 4, ch = i & 15;
+              uint4 w = make_uint4(0u, 0u, 0u, 0u);
+              if (r < nvalid) w = ld_nc_16(base + static_cast<int64_t>(__ldg(trow + tok0 + r)) * row_bytes + ch * 16);
+              const uint32_t dst = tile + (ch >> 3) * kHalfBytes + r * 128 + (((ch & 7) ^ (r & 7)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w) : "memory");
+            }
+            ptx::fence_proxy_async();
+          }
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_expect_tx(full, static_cast<uint32_t>(n_full) * 4096u);
+          __syncwarp();
+          if (lane < n_full) {
+            ptx::tma_load_3d(tile + lane * 2048, map, 0, slot, seg0, full);
+            ptx::tma_load_3d(tile + kHalfBytes + lane * 2048, map, 0, slot, seg0 + 1, full);
+          }
+        };
+        int next = page_slot(0);
+        prof.begin();
+#pragma unroll 1
+        for (int j = 0; j < n; ++j) {
+          const int b = j & 1, u = j >> 1;
+          const int slot = next;
+          if (j + 1 < n) next = page_slot(j + 1);
+          ptx::mbar_wait(bar(K_EMPTY + b), (u & 1) ^ 1);
+          prof.mark(1);
+          load_tile(&tm.k, kbase, smem + kOffK + b * kTileBytes, bar(K_FULL + b), slot, j);
+          prof.mark(2);
+          ptx::mbar_wait(bar(V_EMPTY + b), (u & 1) ^ 1);
+          prof.mark(3);
+          load_tile(&tm.v, vbase, smem + kOffV + b * kTileBytes, bar(V_FULL + b), slot, j);
+          prof.mark(4);
+        }
+      }
+    } else if constexpr (!kFp8) {
       const int64_t row_bytes = p.pool_tok_stride * 2;
       const uint8_t* kbase = reinterpret_cast<const uint8_t*>(p.k_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
       const uint8_t* vbase = reinterpret_cast<const uint8_t*>(p.v_pool) + static_cast<int64_t>(kv_head) * (kTile * 2) + (lane & 15) * 16;
@@ -622,7 +685,13 @@ bool extend_tc_supported(const ExtendParams& p, int D, int kvb) {
 }
 
 namespace {
-using KernelFn = void (*)(const ExtendParams, const int);
+using KernelFn = void (*)(const ExtendParams, const int, const tc::ExtendTmaps);
+
+// B200ATTN_EXTEND_TMA=0 keeps page_size >= 16 pools on the row-gather producers (for A/B timing; default 1)
+bool extend_tma_enabled() {
+  static const bool on = [] { const char* e = getenv("B200ATTN_EXTEND_TMA"); return e ? atoi(e) != 0 : true; }();
+  return on;
+}
 
 template <bool kBf16>
 KernelFn pick_kernel(int emu, bool prof) {
@@ -639,7 +708,22 @@ KernelFn pick_kernel(int emu, bool prof) {
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st) {
   const int emu = (p.exp_emu >= 0 && p.exp_emu <= 3) ? p.exp_emu : 2;
   KernelFn kern;
-  if (p.window >= 0) {
+  static const tc::ExtendTmaps no_maps{};
+  tc::ExtendTmaps maps = no_maps;
+  const bool tma = kvb == 2 && p.page_size >= 16 && p.page_size % 16 == 0 && p.prof == nullptr && extend_tma_enabled();
+  if (tma) {
+    const int64_t row_bytes = p.pool_tok_stride * 2;
+    int rc = encode_pool_tmap(&maps.k, p.k_pool, 2, row_bytes, p.Hkv * 2, 16, 1);
+    if (rc != B200ATTN_OK) return rc;
+    rc = encode_pool_tmap(&maps.v, p.v_pool, 2, row_bytes, p.Hkv * 2, 16, 1);
+    if (rc != B200ATTN_OK) return rc;
+    if (p.window >= 0)
+      kern = q_bf16 ? tc::extend_tc_kernel<true, 0, false, false, false, true, true>
+                    : tc::extend_tc_kernel<false, 0, false, false, false, true, true>;
+    else
+      kern = q_bf16 ? tc::extend_tc_kernel<true, 0, false, false, false, false, true>
+                    : tc::extend_tc_kernel<false, 0, false, false, false, false, true>;
+  } else if (p.window >= 0) {
     if (kvb == 1)
       kern = q_bf16 ? tc::extend_tc_kernel<false, 0, false, true, true, true>
                     : tc::extend_tc_kernel<false, 0, false, true, false, true>;
@@ -658,7 +742,7 @@ int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t s
   dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.grid_order ? nz : p.bs, p.grid_order ? p.bs : nz);
   B2_REQUIRE(grid.y <= 65535 && grid.z <= 65535, B200ATTN_ERR_UNSUPPORTED, "extend: batch %d or %d q tiles exceed the grid",
              p.bs, q_tiles);
-  kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, pair_heads);
+  kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, pair_heads, maps);
   B2_CUDA(cudaGetLastError());
   return B200ATTN_OK;
 }

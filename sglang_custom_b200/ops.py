@@ -190,9 +190,10 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
            plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
            k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
-           lse_out: Optional[torch.Tensor] = None, stage: str = "both") -> torch.Tensor:
+           lse_out: Optional[torch.Tensor] = None, stage: str = "both", page_size: int = 1) -> torch.Tensor:
     """q,out [bs,Hq,D]; pools [P,Hkv,D]; see b200attn_decode in include/b200attn.h.
-    stage: "both" (b200attn_decode), "partial" (stage 1 only) or "merge" (stage 2 only)."""
+    stage: "both" (b200attn_decode), "partial" (stage 1 only) or "merge" (stage 2 only).
+    page_size > 1: the allocator's page size (b200attn_decode_paged; multiples of 16 take the TMA box loads)."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, workspace, lse_out)
     bs, Hq, D = q.shape
     Hkv = k_pool.shape[1]
@@ -214,6 +215,15 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
             workspace.data_ptr(), workspace.numel() * workspace.element_size(), _ptr(lse_out), _stream(q)),
             "b200attn_decode_merge")
         return out
+    if page_size > 1:
+        check(_lib.load().b200attn_decode_paged(
+            q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+            k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+            seq_lens.data_ptr(), _is_i64(seq_lens), bs, Hq, Hkv, D, _dt(q.dtype), _pool_dtype(k_pool, kv_dtype),
+            float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale), plan.data_ptr(), int(n_ctas),
+            workspace.data_ptr(), workspace.numel() * workspace.element_size(), _ptr(lse_out), int(page_size),
+            0 if stage == "both" else 1, _stream(q)), "b200attn_decode_paged")
+        return out
     fn = _lib.load().b200attn_decode if stage == "both" else _lib.load().b200attn_decode_partial
     check(fn(
         q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
@@ -229,7 +239,7 @@ def decode_multiq(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_po
                   req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
                   plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
                   k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
-                  lse_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  lse_out: Optional[torch.Tensor] = None, page_size: int = 1) -> torch.Tensor:
     """q,out [bs,nq,Hq,D] (any request / token strides, head stride D); every one of the nq tokens of request i attends
     to keys [0, seq_lens[i]) -- see b200attn_decode_multiq.  lse_out: fp32 [bs,nq,Hq] (request stride free)."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, workspace, lse_out)
@@ -246,13 +256,17 @@ def decode_multiq(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_po
     if lse_out is not None and (lse_out.dtype != torch.float32 or lse_out.shape != (bs, nq, Hq)
                                 or lse_out.stride(2) != 1 or lse_out.stride(1) != Hq):
         raise B200AttnError("decode_multiq: lse_out must be fp32 [bs,nq,Hq] with contiguous (token, head)")
-    check(_lib.load().b200attn_decode_multiq(
+    args = (
         q.data_ptr(), q.stride(0), q.stride(1), out.data_ptr(), out.stride(0), out.stride(1), k_pool.data_ptr(),
         v_pool.data_ptr(), k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
         req_pool_indices.data_ptr(), seq_lens.data_ptr(), _is_i64(seq_lens), bs, nq, Hq, Hkv, D, _dt(q.dtype),
         _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
         plan.data_ptr(), int(n_ctas), workspace.data_ptr(), workspace.numel() * workspace.element_size(),
-        _ptr(lse_out), lse_out.stride(0) if lse_out is not None else 0, _stream(q)), "b200attn_decode_multiq")
+        _ptr(lse_out), lse_out.stride(0) if lse_out is not None else 0)
+    if page_size > 1:
+        check(_lib.load().b200attn_decode_multiq_paged(*args, int(page_size), _stream(q)), "b200attn_decode_multiq_paged")
+    else:
+        check(_lib.load().b200attn_decode_multiq(*args, _stream(q)), "b200attn_decode_multiq")
     return out
 
 
@@ -284,8 +298,9 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            v_scale: float = 1.0, causal: bool = True, kv_dtype: Optional[torch.dtype] = None,
            impl: int = _lib.EXTEND_AUTO, lse_out: Optional[torch.Tensor] = None, sliding_window_size: int = -1,
            custom_mask: Optional[torch.Tensor] = None, mask_indptr: Optional[torch.Tensor] = None,
-           skip_prefix_custom_mask: bool = True) -> torch.Tensor:
-    """q,out [T,Hq,D]; see b200attn_extend / b200attn_extend_masked in include/b200attn.h.
+           skip_prefix_custom_mask: bool = True, page_size: int = 1) -> torch.Tensor:
+    """q,out [T,Hq,D]; see b200attn_extend / b200attn_extend_masked / b200attn_extend_paged in include/b200attn.h.
+    page_size > 1: the allocator's page size (16-bit pools with page_size % 16 == 0 take TMA box loads).
     sliding_window_size / custom_mask / mask_indptr / skip_prefix_custom_mask carry the meaning they have in
     extend_attention_fwd (triton_ops/extend_attention.py:306-324)."""
     _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, extend_seq_lens,
@@ -306,7 +321,7 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
     if req_pool_indices.dtype != seq_lens.dtype:
         raise B200AttnError("extend: req_pool_indices and seq_lens must share a dtype")
     masked = custom_mask is not None or (sliding_window_size is not None and sliding_window_size > -1)
-    if masked:
+    if masked or page_size > 1:
         if custom_mask is not None:
             _cuda(custom_mask, mask_indptr)
             if custom_mask.dtype not in (torch.bool, torch.uint8) or not custom_mask.is_contiguous():
@@ -314,15 +329,18 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
             if mask_indptr is None or mask_indptr.dtype != torch.int64 or mask_indptr.numel() < bs + 1 \
                     or not mask_indptr.is_contiguous():
                 raise B200AttnError("extend: mask_indptr must be contiguous int64 [bs+1]")
-        check(_lib.load().b200attn_extend_masked(
+        args = (
             q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
             k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
             seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
             extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
             _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale),
             int(bool(causal)), int(impl), int(sliding_window_size if sliding_window_size is not None else -1),
-            _ptr(custom_mask), _ptr(mask_indptr), int(bool(skip_prefix_custom_mask)), _ptr(lse_out), _stream(q)),
-            "b200attn_extend_masked")
+            _ptr(custom_mask), _ptr(mask_indptr), int(bool(skip_prefix_custom_mask)), _ptr(lse_out))
+        if page_size > 1:
+            check(_lib.load().b200attn_extend_paged(*args, int(page_size), _stream(q)), "b200attn_extend_paged")
+        else:
+            check(_lib.load().b200attn_extend_masked(*args, _stream(q)), "b200attn_extend_masked")
         return out
     check(_lib.load().b200attn_extend(
         q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),

@@ -228,3 +228,69 @@ def test_decode_full_size_c2_sampled_oracle_and_relocation_invariance(device):
     ops.decode(c.q, out2, nk, nv, table2, c.req_pool_indices, c.seq_lens, plan, be.n_ctas, ws, c.sm_scale)
     torch.cuda.synchronize()
     assert torch.equal(out2, out)
+
+
+PAGED_CASES = [
+    # bs, Hq, Hkv, lens, fp8, page_size
+    (3, 32, 8, [640, 64, 1000], False, 16),        # bf16, 8 KV heads: one 32 KiB box per page and K/V
+    (4, 8, 1, [5000, 48, 333, 17], True, 16),      # C5 per-rank heads: FP8, 128-byte head rows
+    (3, 64, 8, [1500, 31, 2049], True, 16),        # C5 at TP 1 (token-major consumer, 16 warps)
+    (3, 16, 2, [100, 1, 4097], False, 32),         # page 32: two units per page
+    (2, 16, 4, [777, 4000], True, 64),             # page 64 (test_flashattn_backend.py page_size 64)
+    (2, 16, 1, [300, 129], False, 16),             # G = 16 (head-major consumer, both MMA halves)
+]
+
+
+@pytest.mark.parametrize("bs,Hq,Hkv,lens,fp8,page", PAGED_CASES)
+def test_decode_paged_tile_loads_match_row_gathers(bs, Hq, Hkv, lens, fp8, page, device):
+    """page_size % 16 == 0: the TMA box loads (b200attn_decode_paged) and the row gathers read the same bytes in the
+    same order, so the two outputs are bit-identical -- and both match the oracle.  The rows of every request's last
+    page past its end are poisoned with NaN patterns: whole-page loads must not let them reach the output."""
+    case = synth.make_case(bs, Hq, Hkv, 128, lens, seed=4321 + page + Hq, fp8=fp8, page_size=page,
+                           kv_scale=0.1135 if fp8 else 1.0)
+    kp, vp = H.pool_after_write(case)
+    want = H.oracle_decode(case, kp, vp)
+    c = H.to_device(case, device)
+    dk, dv = kp.to(device).clone(), vp.to(device).clone()
+    # poison: slots of allocated pages that no request position maps to
+    used = torch.zeros(dk.shape[0], dtype=torch.bool, device=device)
+    for i in range(bs):
+        used[c.req_to_token[c.req_pool_indices[i], :lens[i]].long()] = True
+    used[:page] = True
+    if fp8:
+        dk.view(torch.uint8)[~used] = 0x7F
+        dv.view(torch.uint8)[~used] = 0x7F
+    else:
+        dk[~used] = float("nan")
+        dv[~used] = float("nan")
+    n_ctas = 148
+    plan = torch.zeros(ops.decode_plan_bytes(bs, n_ctas) // 4, dtype=torch.int32, device=device)
+    ws = torch.empty(ops.decode_workspace_bytes(n_ctas, Hq, 128) // 4, dtype=torch.float32, device=device)
+    outs = []
+    for ps, min_units in ((page, 4), (1, 4), (page, 1)):
+        ops.decode_plan(c.seq_lens, n_ctas, plan, min_units_per_cta=min_units)
+        out = torch.empty_like(c.q)
+        lse = torch.empty((bs, Hq), dtype=torch.float32, device=device)
+        ops.decode(c.q, out, dk, dv, c.req_to_token, c.req_pool_indices, c.seq_lens, plan, n_ctas, ws, case.sm_scale,
+                   k_scale=case.kv_scale, v_scale=case.kv_scale, kv_dtype=torch.float8_e4m3fn if fp8 else None,
+                   lse_out=lse, page_size=ps)
+        torch.cuda.synchronize()
+        assert torch.isfinite(out.float()).all() and torch.isfinite(lse).all(), f"page_size={ps}: NaN leaked from a page tail"
+        H.assert_close(out, want, what=f"page_size={ps} vs torch_native")
+        outs.append((out, lse))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), "TMA boxes vs row gathers"
+
+
+def test_decode_paged_rejects_bad_arguments(device):
+    case = synth.make_case(1, 8, 1, 128, [64], seed=3, page_size=16)
+    c = H.to_device(case, device)
+    plan = torch.zeros(ops.decode_plan_bytes(1, 4) // 4, dtype=torch.int32, device=device)
+    ws = torch.empty(ops.decode_workspace_bytes(4, 8, 128) // 4, dtype=torch.float32, device=device)
+    ops.decode_plan(c.seq_lens, 4, plan)
+    with pytest.raises(ops.B200AttnError):
+        from sglang_custom_b200 import _lib
+        _lib.check(_lib.load().b200attn_decode_paged(
+            c.q.data_ptr(), c.q.stride(0), c.q.data_ptr(), c.q.stride(0), c.k_pool.data_ptr(), c.v_pool.data_ptr(),
+            c.k_pool.stride(0), c.req_to_token.data_ptr(), c.req_to_token.stride(0), c.req_pool_indices.data_ptr(),
+            c.seq_lens.data_ptr(), 1, 1, 8, 1, 128, 0, 0, 0.1, 0.0, 1.0, 1.0, plan.data_ptr(), 4, ws.data_ptr(),
+            ws.numel() * 4, None, 16, 7, None), "b200attn_decode_paged")

@@ -226,3 +226,42 @@ def test_extend_full_size_c3_sampled_oracle(device):
         want = torch.cat(want_rows)
         got = out[sub.token_rows[rows].to(device)].cpu()
         H.assert_close(got, want, H.EXACT_MAX_ABS_TOL, H.EXACT_MEAN_ABS_TOL, what=f"C3 request {req}", rel=True)
+
+
+PAGED_EXTEND_CASES = [
+    # bs, Hq, Hkv, seq_lens, extend_lens, page_size, dtype, window
+    (2, 32, 8, [512, 400], [256, 400], 16, torch.bfloat16, -1),      # ragged last page (400 % 16 = 0, 512): full pages
+    (3, 8, 2, [1237, 130, 2049], [700, 130, 1000], 16, torch.bfloat16, -1),   # ragged ends, multi-tile prefix
+    (2, 6, 2, [333, 777], [200, 500], 32, torch.float16, -1),        # page 32, G = 3 (two q tiles of one head per CTA)
+    (2, 8, 1, [1500, 900], [300, 257], 64, torch.bfloat16, -1),      # page 64
+    (2, 8, 2, [2000, 1111], [512, 300], 16, torch.bfloat16, 255),    # sliding window on the TMA instantiation
+]
+
+
+@pytest.mark.parametrize("bs,Hq,Hkv,lens,ext,page,dtype,window", PAGED_EXTEND_CASES)
+def test_extend_paged_tile_loads_match_row_gathers(bs, Hq, Hkv, lens, ext, page, dtype, window, device):
+    """page_size % 16 == 0, 16-bit pool: the tcgen05 kernel fed by TMA boxes (b200attn_extend_paged) is bit-identical
+    to the same kernel fed by row gathers, and matches the oracle; pool rows no request position maps to are NaN."""
+    case = synth.make_case(bs, Hq, Hkv, 128, lens, extend_lens=ext, seed=977 + page + Hq, page_size=page, dtype=dtype)
+    kp, vp = H.pool_after_write(case)
+    c = H.to_device(case, device)
+    dk, dv = kp.to(device).clone(), vp.to(device).clone()
+    used = torch.zeros(dk.shape[0], dtype=torch.bool, device=device)
+    for i in range(bs):
+        used[c.req_to_token[c.req_pool_indices[i], :lens[i]].long()] = True
+    used[:page] = True
+    dk[~used] = float("nan")
+    dv[~used] = float("nan")
+    outs = []
+    for ps in (page, 1):
+        out = torch.empty_like(c.q)
+        lse = torch.empty((case.T, Hq), dtype=torch.float32, device=device)
+        ops.extend(c.q, out, dk, dv, c.req_to_token, c.req_pool_indices, c.seq_lens, c.extend_seq_lens,
+                   c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
+                   impl=_lib.EXTEND_TCGEN05, lse_out=lse, sliding_window_size=window, page_size=ps)
+        torch.cuda.synchronize()
+        assert torch.isfinite(out.float()).all() and torch.isfinite(lse).all(), f"page_size={ps}: NaN leaked"
+        outs.append((out, lse))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), "TMA boxes vs row gathers"
+    if window < 0:
+        H.assert_close(outs[0][0], H.oracle_extend(case, kp, vp), what="paged extend vs torch_native")

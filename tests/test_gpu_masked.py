@@ -11,6 +11,8 @@ Tolerance: north_star's bf16 bound (max-abs 2e-2, mean-abs 2e-3); fp16 fixtures 
 """
 from __future__ import annotations
 
+import types
+
 import pytest
 import torch
 
@@ -283,12 +285,14 @@ def test_target_verify_under_cuda_graph(device):
         H.assert_close(out_static.view(case.T, case.Hq, case.D), want, what=f"verify graph replay, mask {seed}")
 
 
-def test_unbuilt_spec_modes_raise(device):
+def test_draft_decode_without_the_multistep_backend_raises(device):
+    reference reads spec_info.kv_indptr / kv_indices there, triton_backend.py:203-205)."""
+    from sglang_custom_b200 import ops
     case = synth.make_case(2, 8, 2, 128, [40, 30], seed=95)
     r = H.Runner(case, device, num_draft_tokens=4)
     fb = r.batch()
-    fb.spec_info = object()  # multi-step draft decode
-    with pytest.raises(NotImplementedError):
+    fb.spec_info = types.SimpleNamespace()
+    with pytest.raises(ops.B200AttnError):
         r.backend.init_forward_metadata(fb)
 
 
