@@ -286,8 +286,8 @@ def test_target_verify_under_cuda_graph(device):
 
 
 def test_draft_decode_without_the_multistep_backend_raises(device):
+    """A decode batch that carries a spec_info is a draft step: its rows come from B200MultiStepDraftBackend (the
     reference reads spec_info.kv_indptr / kv_indices there, triton_backend.py:203-205)."""
-    from sglang_custom_b200 import ops
     case = synth.make_case(2, 8, 2, 128, [40, 30], seed=95)
     r = H.Runner(case, device, num_draft_tokens=4)
     fb = r.batch()
