@@ -8,7 +8,7 @@ import torch
 
 GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 
-ATTN_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("*.pt") if not p.stem.startswith(("kvwrite", "rope", "masked")))
+ATTN_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("*.pt") if not p.stem.startswith(("kvwrite", "rope", "masked", "draft")))
 # sliding window / custom mask: outputs of the reference's Triton kernels (tests/golden/make_golden_masked.py)
 MASKED_EXTEND_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("masked_*.pt") if "decode" not in p.stem)
 MASKED_DECODE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("masked_*decode*.pt"))
