@@ -7,9 +7,11 @@ routes to a CPU or torch implementation.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
+# B200ATTN_LIB: load another build of the same ABI (the development variant libb200attn_dbg.so); never a fallback
+LIB_PATH = Path(os.environ.get("B200ATTN_LIB") or Path(__file__).resolve().parent / "libb200attn.so")
 
 BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
 SCALE_DIV, SCALE_RCP = 0, 1

@@ -130,6 +130,7 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
   using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM>;
   constexpr bool kFp8 = (KVB == 1);
   constexpr int TG = Cfg::TG;
+  static_assert(NSTAGE % TG == 0, "a stage must always serve the same tile group (see decode_stages)");
   static_assert(!kTokM || (kFp8 && kG8), "the token-major consumer is built for FP8 K/V with a GQA group <= 8");
   constexpr bool kMmaBf16 = kQBf16 && !kFp8;  // fp8 K/V are dequantised to f16 (exact)
   constexpr int TS = Cfg::TS, NT = Cfg::NT;
@@ -1012,6 +1013,12 @@ constexpr int decode_stages() {
     if (total + kStatic <= 227 * 1024) break;
     --n;
   }
+  // Two tile groups (CW = 16): the stage count must be EVEN so that a stage always serves the same group.  With an odd
+  // ring a group meets a stage only on every second phase and waits on the same parity each time; a `full` barrier
+  // that is still one fill behind then reads as complete (parity aliasing).  The row gathers complete in issue order,
+  // which hid this; bulk-tensor copies complete out of order -- tile t + 3 can land before tile t -- and large FP8
+  // batches on the paged-tile path read stale stages (found with bench.py's full-size config-5 leg at N = 2).
+  if (CW / kTileWarps > 1) n -= n % (CW / kTileWarps);
   return n;
 }
 
@@ -1313,3 +1320,17 @@ extern "C" B2_EXPORT int b200attn_decode_multiq(B2_MULTIQ_PARAMS, b200attn_strea
 extern "C" B2_EXPORT int b200attn_decode_multiq_paged(B2_MULTIQ_PARAMS, int page_size, b200attn_stream_t stream) {
   return decode_multiq_entry(page_size, B2_MULTIQ_ARGS, stream);
 }
+
+#ifdef B200ATTN_DEBUG_WAIT
+// development build only: timed-out mbarrier waits recorded by the decode kernels (see tc_ptx.cuh); returns the count
+extern "C" B2_EXPORT int b200attn_debug_wait_dump(unsigned int* host_out, int clear) {
+  unsigned int buf[4 * 64 + 1];
+  if (cudaMemcpyFromSymbol(buf, b200attn::ptx::g_wait_dbg, sizeof(buf)) != cudaSuccess) return -1;
+  for (int i = 0; i < 4 * 64 + 1; ++i) host_out[i] = buf[i];
+  if (clear) {
+    unsigned int zero[4 * 64 + 1] = {0};
+    cudaMemcpyToSymbol(b200attn::ptx::g_wait_dbg, zero, sizeof(zero));
+  }
+  return static_cast<int>(buf[0]);
+}
+#endif

@@ -31,12 +31,34 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
   return done;
 }
 // Bounded wait: a protocol bug must end in a trapped launch (an error the host sees), never in a hung GPU.
+#ifdef B200ATTN_DEBUG_WAIT
+// Development build (python -m sglang_custom_b200.build --debug-wait -> libb200attn_dbg.so): a wait that times out is
+// RECORDED (block, thread, barrier address, parity) and abandoned instead of trapping, so the launch ends and the host
+// can read which hand-off broke (b200attn_debug_wait_dump, exported by decode.cu in this build only).
+static __device__ unsigned int g_wait_dbg[4 * 64 + 1];
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 15)) {
+      const unsigned int slot = atomicAdd(&g_wait_dbg[0], 1u);
+      if (slot < 64) {
+        g_wait_dbg[1 + 4 * slot] = blockIdx.x | (blockIdx.y << 16);
+        g_wait_dbg[2 + 4 * slot] = threadIdx.x;
+        g_wait_dbg[3 + 4 * slot] = bar;
+        g_wait_dbg[4 + 4 * slot] = parity;
+      }
+      return;
+    }
+  }
+}
+#else
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > (1u << 20)) __trap();  // ~4 s of try_wait time-outs
   }
 }
+#endif
 
 // the mbarrier receives one arrival when every cp.async issued so far by this thread has landed (no count increment:
 // the barrier is initialised with the number of producer threads)

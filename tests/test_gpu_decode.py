@@ -294,3 +294,26 @@ def test_decode_paged_rejects_bad_arguments(device):
             c.k_pool.stride(0), c.req_to_token.data_ptr(), c.req_to_token.stride(0), c.req_pool_indices.data_ptr(),
             c.seq_lens.data_ptr(), 1, 1, 8, 1, 128, 0, 0, 0.1, 0.0, 1.0, 1.0, plan.data_ptr(), 4, ws.data_ptr(),
             ws.numel() * 4, None, 16, 7, None), "b200attn_decode_paged")
+
+
+def test_decode_paged_large_fp8_batch_two_tile_groups(device):
+    """Regression (round 2): the 16-warp FP8 consumer runs two tile groups over the stage ring.  With an odd ring a
+    group met a stage on every second phase only -- the same parity every time -- and bulk-tensor copies complete out
+    of order, so a `full` barrier one fill behind read as complete: stale stages at best, a faulted launch at worst
+    (bs 64 x 8000 tokens, 64/8 heads, page 16; small cases never showed it).  Boxes and row gathers must agree bit for
+    bit at a size where the ring wraps hundreds of times per CTA."""
+    bs, Hq, Hkv, L = 64, 64, 8, 8000
+    case = synth.make_case_device(bs, Hq, Hkv, 128, [L] * bs, device, page_size=16, fp8=True, kv_scale=0.1135, seed=77)
+    n_ctas = 148
+    plan = torch.zeros(ops.decode_plan_bytes(bs, n_ctas) // 4, dtype=torch.int32, device=device)
+    ws = torch.empty(ops.decode_workspace_bytes(n_ctas, Hq, 128) // 4, dtype=torch.float32, device=device)
+    ops.decode_plan(case.seq_lens, n_ctas, plan)
+    outs = []
+    for ps in (1, 16, 16):
+        out = torch.empty_like(case.q)
+        ops.decode(case.q, out, case.k_pool, case.v_pool, case.req_to_token, case.req_pool_indices, case.seq_lens, plan,
+                   n_ctas, ws, case.sm_scale, k_scale=case.kv_scale, v_scale=case.kv_scale,
+                   kv_dtype=torch.float8_e4m3fn, page_size=ps)
+        torch.cuda.synchronize()
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
