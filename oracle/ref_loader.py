@@ -69,7 +69,16 @@ def load():
     _stub("sglang.srt.layers.radix_attention", AttentionType=AttentionType, RadixAttention=object)
     _stub("sglang.srt.model_executor.forward_batch_info", ForwardBatch=object, ForwardMode=object)
     _stub("sglang.srt.model_executor.cuda_graph_runner", get_is_capture_mode=lambda: False)
-    _stub("sglang.srt.torch_memory_saver_adapter", TorchMemorySaverAdapter=object)
+    class _NoMemorySaver:  # stand-in for torch_memory_saver_adapter.TorchMemorySaverAdapter (an optional dependency):
+        @staticmethod      # create(enable) -> object whose region(tag) is a no-op context manager
+        def create(enable=False):
+            return _NoMemorySaver()
+
+        def region(self, *a, **k):
+            import contextlib
+            return contextlib.nullcontext()
+
+    _stub("sglang.srt.torch_memory_saver_adapter", TorchMemorySaverAdapter=_NoMemorySaver)
     _stub("sglang.srt.constants", GPU_MEMORY_TYPE_KV_CACHE="kv_cache")
     _stub("sglang.srt.utils", get_bool_env_var=lambda *a, **k: False, is_cuda=lambda: False,
           is_npu=lambda: False, next_power_of_2=lambda n: 1 << (max(int(n), 1) - 1).bit_length())
