@@ -73,11 +73,16 @@ constexpr int kMaxSeg = 32;
 
 // CW consumer warps = TG = CW / 8 tile groups of 8 warps; group g consumes the tiles t with t % TG == g, so that with
 // CW = 16 two stages of the ring are being consumed at any time (four consumer warps per SM sub-partition).
-template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE, int CW = 8, bool kTokM = false>
+// kBig (token-major FP8 consumer only): all CW = 16 consumer warps share one tile -- a stage of 64 KiB instead of two
+// tile groups over 32 KiB stages.  An FP8 row is half as long as a bf16 row, so a 16-token tile is half the bytes and the
+// per-tile fixed cost of the gather side (slot ring, producer barrier, mbarrier hand-overs) weighs twice as much: ncu
+// showed the 16-warp kernel's consumers waiting for data with DRAM at 74 % whatever the page table looked like.
+template <int D, int HB, int KVB /*bytes per kv elem*/, int NSTAGE, int CW = 8, bool kTokM = false, bool kBig = false>
 struct DecodeCfg {
-  static constexpr int TG = CW / kTileWarps;         // tile groups
+  static constexpr int TW = (kTokM && kBig) ? CW : kTileWarps;  // consumer warps that share one tile
+  static constexpr int TG = CW / TW;                 // tile groups
   static constexpr int THREADS = CW * 32 + kProducerThreads;
-  static constexpr int TS = kTileWarps / HB;         // token sub-tiles (warps) per head and tile
+  static constexpr int TS = TW / HB;                 // token sub-tiles (warps) per head and tile
   static constexpr int NT = 16 * TS;                 // tokens per tile
   static constexpr int HEADB = D * KVB;              // bytes of one head row
   static constexpr int ROWB = HB * HEADB;            // bytes gathered per token (K or V)
@@ -93,7 +98,10 @@ struct DecodeCfg {
   // cross-warp merge buffer of the TS * TG warps of a head (dedicated: the producers refill stages asynchronously).
   // Token-major consumers (kTokM) park their whole register state lane by lane: (D/16*4 + 4) floats per lane.
   static constexpr int RED_SLOT_F = kTokM ? (D / 16 * 4 + 4) * 32 : RED_ROWS * (D + 2);
-  static constexpr int REDB = (TS * TG > 1) ? (CW / 2) * RED_SLOT_F * 4 : 0;
+  // slots of the merge buffer; a merge round with more writers than slots runs in passes (kBig: the 64 KiB stages leave
+  // room for four slots)
+  static constexpr int RED_SLOTS = (kTokM && kBig) ? 4 : CW / 2;
+  static constexpr int REDB = (TS * TG > 1) ? RED_SLOTS * RED_SLOT_F * 4 : 0;
   static constexpr int IDXB = 2 * NT * 4;            // double-buffered token-slot ring
   static constexpr int BARB = 2 * NSTAGE * 8;        // full[NSTAGE], empty[NSTAGE]
   static constexpr int OFF_RED = NSTAGE * STAGEB;
@@ -124,10 +132,11 @@ __device__ __forceinline__ void named_barrier(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE, int CW, bool kTokM, bool kTma>
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, int NSTAGE, int CW, bool kTokM, bool kTma, bool kBig = false>
 __global__ void __launch_bounds__(CW * 32 + kProducerThreads, 1)
 decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
-  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM>;
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM, kBig>;
+  constexpr int TW = Cfg::TW;
   constexpr bool kFp8 = (KVB == 1);
   constexpr int TG = Cfg::TG;
   static_assert(NSTAGE % TG == 0, "a stage must always serve the same tile group (see decode_stages)");
@@ -175,7 +184,7 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
     next_unit_sh = u_begin;
     for (int s = 0; s < NSTAGE; ++s) {
       ptx::mbar_init(full_bar(s), kTma ? 1 : kProducerThreads);
-      ptx::mbar_init(empty_bar(s), kTileWarps);
+      ptx::mbar_init(empty_bar(s), TW);
     }
     ptx::fence_mbar_init();
   }
@@ -337,9 +346,9 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
       const int n_segs = n_segs_sh;
       if (n_segs == 0) break;
       // ============================================================ consumers
-      const int tg = warp / kTileWarps;            // tile group: consumes the tiles with tile_no % TG == tg
-      const int hb = (warp % kTileWarps) % HB;     // head within the CTA's head block
-      const int ts = (warp % kTileWarps) / HB;     // token sub-tile inside a tile
+      const int tg = warp / TW;            // tile group: consumes the tiles with tile_no % TG == tg
+      const int hb = (warp % TW) % HB;     // head within the CTA's head block
+      const int ts = (warp % TW) / HB;     // token sub-tile inside a tile
       const int qd = lane & 3;    // quad lane
       const int row = lane >> 2;  // MMA row 0..7
       const int kv_head = blockIdx.y * HB + hb;
@@ -781,37 +790,44 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
           if constexpr (TS * TG > 1) {
             const int tsa = tg * TS + ts;
             constexpr int SLOT = Cfg::RED_SLOT_F;
+            constexpr int RS = Cfg::RED_SLOTS;
   #pragma unroll
             for (int half = TS * TG / 2; half >= 1; half >>= 1) {
-              consumer_barrier();
-              if (tsa >= half && tsa < 2 * half) {
-                float* dst = red_buf + ((tsa - half) * HB + hb) * SLOT + lane;
+              // the half * HB warps with tsa in [half, 2 half) hand their state to the warps below them, RS at a time
   #pragma unroll
-                for (int nb = 0; nb < NB; ++nb) {
+              for (int pass = 0; pass * RS < half * HB; ++pass) {
+                consumer_barrier();
+                const int wslot = (tsa - half) * HB + hb;
+                if (tsa >= half && tsa < 2 * half && wslot / RS == pass) {
+                  float* dst = red_buf + (wslot % RS) * SLOT + lane;
   #pragma unroll
-                  for (int e = 0; e < 4; ++e) dst[(nb * 4 + e) * 32] = o[nb][e];
+                  for (int nb = 0; nb < NB; ++nb) {
+  #pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[(nb * 4 + e) * 32] = o[nb][e];
+                  }
+                  dst[(NB * 4 + 0) * 32] = mh0; dst[(NB * 4 + 1) * 32] = mh1;
+                  dst[(NB * 4 + 2) * 32] = lh0; dst[(NB * 4 + 3) * 32] = lh1;
                 }
-                dst[(NB * 4 + 0) * 32] = mh0; dst[(NB * 4 + 1) * 32] = mh1;
-                dst[(NB * 4 + 2) * 32] = lh0; dst[(NB * 4 + 3) * 32] = lh1;
-              }
-              consumer_barrier();
-              if (tsa < half) {
-                const float* src = red_buf + (tsa * HB + hb) * SLOT + lane;
-                const float om0 = src[(NB * 4 + 0) * 32], om1 = src[(NB * 4 + 1) * 32];
-                const float mn0 = fmaxf(mh0, om0), mn1 = fmaxf(mh1, om1);
-                const float a0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(mh0 - mn0);
-                const float c0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(om0 - mn0);
-                const float a1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(mh1 - mn1);
-                const float c1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(om1 - mn1);
-                mh0 = mn0; mh1 = mn1;
-                lh0 = lh0 * a0 + src[(NB * 4 + 2) * 32] * c0;
-                lh1 = lh1 * a1 + src[(NB * 4 + 3) * 32] * c1;
+                consumer_barrier();
+                const int rslot = tsa * HB + hb;
+                if (tsa < half && rslot / RS == pass) {
+                  const float* src = red_buf + (rslot % RS) * SLOT + lane;
+                  const float om0 = src[(NB * 4 + 0) * 32], om1 = src[(NB * 4 + 1) * 32];
+                  const float mn0 = fmaxf(mh0, om0), mn1 = fmaxf(mh1, om1);
+                  const float a0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(mh0 - mn0);
+                  const float c0 = (mn0 == -INFINITY) ? 0.f : fast_exp2(om0 - mn0);
+                  const float a1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(mh1 - mn1);
+                  const float c1 = (mn1 == -INFINITY) ? 0.f : fast_exp2(om1 - mn1);
+                  mh0 = mn0; mh1 = mn1;
+                  lh0 = lh0 * a0 + src[(NB * 4 + 2) * 32] * c0;
+                  lh1 = lh1 * a1 + src[(NB * 4 + 3) * 32] * c1;
   #pragma unroll
-                for (int nb = 0; nb < NB; ++nb) {
-                  o[nb][0] = o[nb][0] * a0 + src[(nb * 4 + 0) * 32] * c0;
-                  o[nb][1] = o[nb][1] * a1 + src[(nb * 4 + 1) * 32] * c1;
-                  o[nb][2] = o[nb][2] * a0 + src[(nb * 4 + 2) * 32] * c0;
-                  o[nb][3] = o[nb][3] * a1 + src[(nb * 4 + 3) * 32] * c1;
+                  for (int nb = 0; nb < NB; ++nb) {
+                    o[nb][0] = o[nb][0] * a0 + src[(nb * 4 + 0) * 32] * c0;
+                    o[nb][1] = o[nb][1] * a1 + src[(nb * 4 + 1) * 32] * c1;
+                    o[nb][2] = o[nb][2] * a0 + src[(nb * 4 + 2) * 32] * c0;
+                    o[nb][3] = o[nb][3] * a1 + src[(nb * 4 + 3) * 32] * c1;
+                  }
                 }
               }
             }
@@ -1000,16 +1016,17 @@ __global__ void __launch_bounds__(kMergeWarps * 32) decode_merge_kernel(const De
 }
 
 // stage count: as many stages as fit next to the merge buffer (at least 2, at most 6; 3 are enough for 64 KiB stages)
-template <int D, int HB, int KVB, int CW, bool kTokM>
+template <int D, int HB, int KVB, int CW, bool kTokM, bool kBig = false>
 constexpr int decode_stages() {
+  constexpr int TW = (kTokM && kBig) ? CW : kTileWarps;
   constexpr int kStatic = 2048;
-  int n = (128 * D * KVB * 2 >= 65536) ? 3 : 6;
+  int n = (2 * (16 * (TW / HB)) * HB * D * KVB >= 65536) ? 3 : 6;
   while (n > 2) {
-    const int stageb = 2 * (16 * (kTileWarps / HB)) * HB * D * KVB;
-    const int tstg = (kTileWarps / HB) * (CW / kTileWarps);
+    const int stageb = 2 * (16 * (TW / HB)) * HB * D * KVB;
+    const int tstg = (TW / HB) * (CW / TW);
     const int slot_f = kTokM ? (D / 16 * 4 + 4) * 32 : 16 * (D + 2);
-    const int redb = tstg > 1 ? (CW / 2) * slot_f * 4 : 0;
-    const int total = n * stageb + redb + 2 * 16 * (kTileWarps / HB) * 4 + 2 * n * 8 + 128 + 1024;
+    const int redb = tstg > 1 ? ((kTokM && kBig) ? 4 : CW / 2) * slot_f * 4 : 0;
+    const int total = n * stageb + redb + 2 * 16 * (TW / HB) * 4 + 2 * n * 8 + 128 + 1024;
     if (total + kStatic <= 227 * 1024) break;
     --n;
   }
@@ -1018,7 +1035,7 @@ constexpr int decode_stages() {
   // that is still one fill behind then reads as complete (parity aliasing).  The row gathers complete in issue order,
   // which hid this; bulk-tensor copies complete out of order -- tile t + 3 can land before tile t -- and large FP8
   // batches on the paged-tile path read stale stages (found with bench.py's full-size config-5 leg at N = 2).
-  if (CW / kTileWarps > 1) n -= n % (CW / kTileWarps);
+  if (CW / TW > 1) n -= n % (CW / TW);
   return n;
 }
 
@@ -1058,11 +1075,11 @@ static int decode_tmaps(const DecodeParams& p, int kvb, int D, int HB, const Dec
   return B200ATTN_OK;
 }
 
-template <int D, int HB, int KVB, bool kQBf16, bool kG8, int CW, bool kTokM, bool kTma>
+template <int D, int HB, int KVB, bool kQBf16, bool kG8, int CW, bool kTokM, bool kTma, bool kBig = false>
 static int launch_decode_cw(const DecodeParams& p_in, int head_groups, cudaStream_t st) {
   constexpr int kStatic = 2048;
-  constexpr int NSTAGE = decode_stages<D, HB, KVB, CW, kTokM>();
-  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM>;
+  constexpr int NSTAGE = decode_stages<D, HB, KVB, CW, kTokM, kBig>();
+  using Cfg = DecodeCfg<D, HB, KVB, NSTAGE, CW, kTokM, kBig>;
   static_assert(Cfg::SMEM + kStatic <= 227 * 1024, "decode staging exceeds the shared memory of one CTA");
   DecodeParams p = p_in;
   static const DecodeTmaps no_maps{};
@@ -1072,7 +1089,7 @@ static int launch_decode_cw(const DecodeParams& p_in, int head_groups, cudaStrea
     if (rc != B200ATTN_OK) return rc;
     p.tma_order = 0;
   }
-  auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE, CW, kTokM, kTma>;
+  auto kern = decode_kernel<D, HB, KVB, kQBf16, kG8, NSTAGE, CW, kTokM, kTma, kBig>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
@@ -1090,10 +1107,23 @@ static bool fp8_tokm_enabled() {
   return on;
 }
 
+// B200ATTN_DECODE_FP8_BIG=0 keeps the two-tile-group form of the FP8 token-major kernel (for A/B timing; default 1)
+static int fp8_big_level() {
+  static const int lv = [] { const char* e = getenv("B200ATTN_DECODE_FP8_BIG"); return e ? atoi(e) : 1; }();
+  return lv;
+}
+
 template <int D, int HB, int KVB, bool kQBf16, bool kG8, bool kTma>
 static int launch_decode_t(const DecodeParams& p, int head_groups, cudaStream_t st) {
   if constexpr (KVB == 1 && kG8) {
-    if (fp8_tokm_enabled()) return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma>(p, head_groups, st);
+    if (fp8_tokm_enabled()) {
+      // 64 KiB stages shared by all 16 warps where a tile stays short (HB >= 4: 32 / 64 tokens)
+      if constexpr (D == 128 && HB >= 2) {  // (HB = 1 would need 256 slots per tile from 128 producer threads)
+        if (fp8_big_level() >= (HB >= 4 ? 1 : 2))
+          return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma, true>(p, head_groups, st);
+      }
+      return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma>(p, head_groups, st);
+    }
   }
   return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 8, false, kTma>(p, head_groups, st);
 }
