@@ -269,18 +269,32 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
       const uint8_t* kcol = kpool + cr * 16;
       const uint8_t* vcol = vpool + cr * 16;
       int i_seg = 0, i_tile = 0;  // next tile whose token slots get fetched
-      int32_t pend = -1;
+      constexpr int SPT = (NT + kProducerThreads - 1) / kProducerThreads;  // token slots fetched per producer thread and tile
+      int32_t pend[SPT];
+#pragma unroll
+      for (int i = 0; i < SPT; ++i) pend[i] = -1;
       auto fetch = [&]() {
         if (i_seg >= n_segs) return;
-        if (ptid < NT) {
-          const Segment& s = segs[i_seg];
-          const int tok = s.tok_begin + i_tile * NT + ptid;
-          pend = (tok < s.tok_end) ? __ldg(p.req_to_token + s.table_off + tok) : -1;
+        const Segment& s = segs[i_seg];
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) {
+          const int tt = ptid + i * kProducerThreads;
+          if (tt < NT) {
+            const int tok = s.tok_begin + i_tile * NT + tt;
+            pend[i] = (tok < s.tok_end) ? __ldg(p.req_to_token + s.table_off + tok) : -1;
+          }
         }
         if (++i_tile >= seg_tiles(i_seg)) { i_tile = 0; ++i_seg; }
       };
+      auto publish = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) {
+          const int tt = ptid + i * kProducerThreads;
+          if (tt < NT) idx_ring[buf * NT + tt] = pend[i];
+        }
+      };
       fetch();
-      if (ptid < NT) idx_ring[ptid] = pend;
+      publish(0);
       named_barrier(2, kProducerThreads);
       fetch();
       int cur = 0;
@@ -303,7 +317,7 @@ decode_kernel(const DecodeParams p, const __grid_constant__ DecodeTmaps tm) {
             cp_async16(v_s + dst, vcol + src, valid);
           }
           ptx::cp_async_mbar_arrive_noinc(full_bar(stage));
-          if (ptid < NT) idx_ring[(cur ^ 1) * NT + ptid] = pend;  // slots of the next tile (fetched a tile ago)
+          publish(cur ^ 1);  // slots of the next tile (fetched a tile ago)
           fetch();
           named_barrier(2, kProducerThreads);
           cur ^= 1;
@@ -1107,7 +1121,8 @@ static bool fp8_tokm_enabled() {
   return on;
 }
 
-// B200ATTN_DECODE_FP8_BIG=0 keeps the two-tile-group form of the FP8 token-major kernel (for A/B timing; default 1)
+// B200ATTN_DECODE_FP8_BIG: 0 = two tile groups over 32 KiB stages (the form before round 2's last change), 1 = 64 KiB
+// stages for head blocks >= 2 (default), 2 = for every head block
 static int fp8_big_level() {
   static const int lv = [] { const char* e = getenv("B200ATTN_DECODE_FP8_BIG"); return e ? atoi(e) : 1; }();
   return lv;
@@ -1117,9 +1132,10 @@ template <int D, int HB, int KVB, bool kQBf16, bool kG8, bool kTma>
 static int launch_decode_t(const DecodeParams& p, int head_groups, cudaStream_t st) {
   if constexpr (KVB == 1 && kG8) {
     if (fp8_tokm_enabled()) {
-      // 64 KiB stages shared by all 16 warps where a tile stays short (HB >= 4: 32 / 64 tokens)
-      if constexpr (D == 128 && HB >= 2) {  // (HB = 1 would need 256 slots per tile from 128 producer threads)
-        if (fp8_big_level() >= (HB >= 4 ? 1 : 2))
+      // 64 KiB stages shared by all 16 warps (32 / 64 / 128 tokens per tile for 8 / 4 / 2 heads per CTA; one head per
+      // CTA -- 256-token tiles -- gains 2 % at C4 / TP 8 and is left to B200ATTN_DECODE_FP8_BIG=2)
+      if constexpr (D == 128) {
+        if (fp8_big_level() >= (HB >= 2 ? 1 : 2))
           return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma, true>(p, head_groups, st);
       }
       return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma>(p, head_groups, st);
