@@ -129,6 +129,9 @@ class B200AttnBackend(AttentionBackend):
         self.scale_mode = _lib.SCALE_DIV
         self.writeback_scaled_kv = False
         self.verify_via_decode = True  # TARGET_VERIFY: cached-prefix part on the split-KV decode kernel
+        # ... as long as it takes at most this many passes of 16 (draft token, q head) rows: a pass streams the prefix once
+        # (0.65 ms at bs 256 / ctx 4096, profiles/r01_time_masked_verify.txt), the masked extend kernel alone takes 6.9 ms
+        self.verify_max_passes = 8
         # MIXED: decode tail on a side stream, concurrent with the prefill rows (False: serial; True: tail launched
         # first; 2: prefill launched first).  C5 per-rank shape: 0.823 -> 0.731 ms per layer, bit-identical.
         self.overlap_mixed = 2
@@ -477,7 +480,7 @@ class B200AttnBackend(AttentionBackend):
             rpi = rpi[:md.bs]
             nd, Hq = md.max_extend_len, layer.tp_q_head_num
             per_pass = 16 // (Hq // layer.tp_k_head_num) if Hq // layer.tp_k_head_num <= 16 else 0
-            if self.verify_via_decode and causal and per_pass > 0 and -(-nd // per_pass) <= 4 \
+            if self.verify_via_decode and causal and per_pass > 0 and -(-nd // per_pass) <= self.verify_max_passes \
                     and self.verify_workspace is not None and o3.is_contiguous():
                 # HBM-bound like decode: every draft token sees the whole cached prefix, so that part is ONE
                 # split-KV pass per 16 (token, head) rows over the page table (b200attn_decode_multiq); the few
