@@ -21,7 +21,7 @@
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
  *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
  *   b200attn_decode_multiq       cached-prefix part of TARGET_VERIFY batches (triton_backend.py:227-264)
- *   b200attn_decode_paged, b200attn_decode_multiq_paged, b200attn_extend_paged
+ *   b200attn_decode_paged, b200attn_decode_multiq_paged, b200attn_extend_paged, b200attn_extend_split
  *                                the same three for paged pools (mem_cache/allocator.py:444-447 slot layout)
  *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
  *   b200attn_extend_masked       triton_ops/extend_attention.py:158-175,236-247 (sliding window, custom mask)
@@ -51,7 +51,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_VERSION 210 /* 0.2.1: + decode_paged / decode_multiq_paged / extend_paged (page_size >= 16: TMA box loads) */
+#define B200ATTN_VERSION 220 /* 0.2.2: + extend_split (KV splits of the tcgen05 extend kernel); 0.2.1: + *_paged (TMA box loads) */
 
 /* element types */
 #define B200ATTN_BF16 0
@@ -309,6 +309,25 @@ int b200attn_extend_paged(const void* q, int64_t q_tok_stride, void* out, int64_
                            float logit_cap, float k_scale, float v_scale, int causal, int impl, int sliding_window_size,
                            const uint8_t* custom_mask, const int64_t* mask_indptr, int skip_prefix_custom_mask,
                            float* lse_out, int page_size, b200attn_stream_t stream);
+
+/* b200attn_extend_paged with the K/V range of every (request, head pair, 128 q rows) item cut into kv_splits shares
+ * that run as separate CTAs of the tcgen05 kernel; each writes a normalised partial + LSE into `workspace`, a second
+ * kernel merges them into out / lse_out.  For batches whose items do not fill the GPU -- a chunked-prefill row over a
+ * long radix prefix (triton_backend.py:632-685 with extend_prefix_lens >> extend_seq_lens), head-partitioned ranks
+ * (configs/model_config.py:342-349) -- where one item per CTA leaves SMs idle for the length of the longest row.
+ * Plain batches only: no sliding window, no custom mask; D == 128, logit_cap == 0 (the tcgen05 kernel); otherwise
+ * B200ATTN_ERR_UNSUPPORTED.  T = total new tokens (rows of q / out).  kv_splits == 1 is b200attn_extend_paged.
+ * Partials are stored in the q dtype, so results differ from the unsplit call by one extra rounding (inside the
+ * parity bound, not bit-identical). */
+size_t b200attn_extend_split_workspace_bytes(int T, int Hq, int D, int kv_splits);
+int b200attn_extend_split(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                          const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                          const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                          const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens,
+                          const int32_t* extend_prefix_lens, const int32_t* extend_start_loc, int bs,
+                          int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+                          float k_scale, float v_scale, int causal, float* lse_out, int page_size, int T, int kv_splits,
+                          void* workspace, size_t workspace_bytes, b200attn_stream_t stream);
 #define B200ATTN_WINDOW_NEW_TOKENS_ONLY (-2)
 #define B200ATTN_EXTEND_AUTO 0
 #define B200ATTN_EXTEND_TCGEN05 1 /* tcgen05/TMEM kernel (D == 128, bf16/f16 KV) */

@@ -44,6 +44,35 @@ for name, impl in (("mma", _lib.EXTEND_MMA), ("tc", _lib.EXTEND_TCGEN05)):
         for i in range(min(n, 24)):
             b, t, bar, par = buf[1 + 4 * i:5 + 4 * i]
             print(f"   block ({b & 0xffff},{b >> 16}) thread {t} (warp {t // 32}) bar 0x{bar:x} (#{(bar & 0xff) // 8}) parity {par}")
+for a in sys.argv:
+    if a.startswith("splits="):
+        S = int(a.split("=")[1])
+        ws = torch.empty(ops.extend_split_workspace_bytes(c.q.shape[0], Hq, 128, S), dtype=torch.uint8, device=dev)
+        out = torch.zeros_like(c.q)
+        lse = torch.zeros((c.q.shape[0], Hq), dtype=torch.float32, device=dev)
+        ops.extend(c.q, out, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.seq_lens, c.extend_seq_lens,
+                   c.extend_prefix_lens, c.extend_start_loc, max(ext), c.sm_scale, k_scale=c.kv_scale, v_scale=c.kv_scale,
+                   kv_dtype=torch.float8_e4m3fn if fp8 else None, lse_out=lse, page_size=page, kv_splits=S, workspace=ws)
+        torch.cuda.synchronize()
+        d = (out.float() - outs["tc"][0].float()).abs()
+        dl = (lse - outs["tc"][1]).abs()
+        print(f"splits={S} vs tc: out max {float(d.max()):.5f} mean {float(d.mean()):.6f}   lse max {float(dl.max()):.5f}  nan {int(torch.isnan(out.float()).sum())}")
+        import time
+        for nm, kw in (("unsplit", {}), (f"splits={S}", dict(kv_splits=S, workspace=ws))):
+            fn = lambda: ops.extend(c.q, out, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.seq_lens,  # noqa: E731
+                                    c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, max(ext), c.sm_scale,
+                                    k_scale=c.kv_scale, v_scale=c.kv_scale, kv_dtype=torch.float8_e4m3fn if fp8 else None,
+                                    page_size=page, impl=_lib.EXTEND_TCGEN05 if not kw else _lib.EXTEND_AUTO, **kw)
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            print(f"   {nm}: {e0.elapsed_time(e1) / 10 * 1e3:.1f} us")
 d = (outs["tc"][0].float() - outs["mma"][0].float()).abs()
 dl = (outs["tc"][1] - outs["mma"][1]).abs()
 print(f"tc vs mma: out max {float(d.max()):.5f} mean {float(d.mean()):.6f}   lse max {float(dl.max()):.5f}  nan {int(torch.isnan(outs['tc'][0].float()).sum())}", flush=True)

@@ -56,6 +56,9 @@ SIGNATURES = {
                                     _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
     "b200attn_extend_paged": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
                                    _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _i, _i, _i, _vp, _vp, _i, _vp, _i, _vp]),
+    "b200attn_extend_split_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "b200attn_extend_split": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,
+                                   _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _i, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "b200attn_check_loc": (_i, [_vp, _i, _i64, _i64, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),

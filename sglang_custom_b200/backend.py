@@ -13,6 +13,8 @@ There is no fallback path: a missing library or an unsupported feature raises.
 """
 from __future__ import annotations
 
+import os
+
 from abc import ABC, abstractmethod
 from dataclasses import dataclass
 from typing import Optional
@@ -73,6 +75,8 @@ class ForwardMetadata:
     # number of q rows that belong to the prefill requests (sum of their extend lens, from the host list): the tail
     # rows start there even when q carries padded rows behind them (DP attention / num_token_non_padded)
     n_extend_tokens: int = -1
+    # KV splits of the prefill rows' extend kernel (chosen on the host from extend_*_lens_cpu, see _choose_kv_splits)
+    kv_splits: int = 1
     # TARGET_VERIFY (speculative decoding): every request contributes num_draft_tokens query rows over its
     # seq_lens cached tokens; built on the device, no host sync (triton_backend.py:227-264)
     extend_seq_lens: Optional[torch.Tensor] = None
@@ -128,6 +132,9 @@ class B200AttnBackend(AttentionBackend):
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.scale_mode = _lib.SCALE_DIV
         self.writeback_scaled_kv = False
+        # prefill rows: 0 = choose KV splits per batch (_choose_kv_splits), 1 = never, n = always n
+        self.extend_kv_splits = int(os.environ.get("B200ATTN_EXTEND_KV_SPLITS", "0"))
+        self._split_ws = None
         self.verify_via_decode = True  # TARGET_VERIFY: cached-prefix part on the split-KV decode kernel
         # ... as long as it takes at most this many passes of 16 (draft token, q head) rows: a pass streams the prefix once
         # (0.65 ms at bs 256 / ctx 4096, profiles/r01_time_masked_verify.txt), the masked extend kernel alone takes 6.9 ms
@@ -140,7 +147,6 @@ class B200AttnBackend(AttentionBackend):
         # (layer_id, id(forward_batch)) of the last fused RoPE + KV write (rotary.forward_fused_kv): the only case in
         # which forward_* may be called with k/v and save_kv_cache=False (see _require_kv_in_pool)
         self._kv_written = None
-        import os
         self.check_loc = os.environ.get("B200ATTN_CHECK_LOC", "0") not in ("", "0")
 
     # ------------------------------------------------------------------ buffers
@@ -205,8 +211,65 @@ class B200AttnBackend(AttentionBackend):
         if n_tail:
             # a query with extend_len 1 at position L-1 sees all L keys: exactly a decode row
             self._plan_decode(forward_batch.seq_lens[bs - n_tail:])
+        kv_splits = 1
+        pre_cpu = getattr(forward_batch, "extend_prefix_lens_cpu", None)
+        if ext_cpu is not None and pre_cpu is not None and self.extend_kv_splits != 1:
+            kv_splits = self._choose_kv_splits(ext_cpu[:len(ext_cpu) - n_tail], list(pre_cpu)[:len(ext_cpu) - n_tail])
         self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend,
-                                                n_decode_tail=n_tail, n_extend_tokens=t_ext)
+                                                n_decode_tail=n_tail, n_extend_tokens=t_ext, kv_splits=kv_splits)
+
+    def _choose_kv_splits(self, ext, pre) -> int:
+        """How many shares the K/V range of every prefill item is cut into (b200attn_extend_split).  The tcgen05 extend
+        kernel has one CTA per (request, head pair, 128 q rows); a few long rows -- chunked prefill over a long prefix,
+        few heads per rank -- leave SMs idle for the length of the longest item.  When the grid is small (< 4 CTAs per
+        SM) the launch is simulated on the host for a few split factors: CTAs in block-index order onto the first free
+        SM, cost of a CTA = its 128-key tiles + 3 (launch, Q load, fill, drain, epilogue; one tile = 1.84 us measured),
+        plus the merge pass.  Host lists only, no sync; 0 = auto (default), n > 1 forces n."""
+        if self.extend_kv_splits > 1:
+            return self.extend_kv_splits
+        if not ext or max(ext) < 128:
+            return 1
+        G = self.num_head // max(1, self.num_kv_head)
+        hp = self.num_head // 2 if G % 2 == 0 else self.num_head
+        rows_per_item = 128 if G % 2 == 0 else 256
+        sms = self.n_ctas
+        groups, items, longest, T = [], 0, 0, 0  # groups: tiles of the hp identical items of (request, q tile), launch order
+        for e, p_ in zip(ext, pre):
+            if e <= 0:
+                continue
+            nq = -(-e // rows_per_item)
+            items += hp * nq
+            if items >= 4 * sms:
+                return 1  # the GPU is filled several times over: nothing to gain
+            per_req = [(p_ + min((z + 1) * rows_per_item, e) + 127) // 128 for z in range(nq - 1, -1, -1)]  # heavy first
+            groups.append(per_req)
+            longest = max(longest, per_req[0])
+            T += e
+        if items == 0 or longest < 16:
+            return 1
+        import heapq
+        c = 3.0
+        merge_per_split = T * self.num_head * 256 / 5e6 / 1.84  # bytes of one partial / (5 TB/s), in tile units
+
+        def makespan(S: int) -> float:
+            free = [0.0] * sms
+            for per_req in groups:
+                for _ in range(S):
+                    for n in per_req:
+                        cost = n / S + c
+                        for _ in range(hp):
+                            heapq.heapreplace(free, free[0] + cost)
+            return max(free) + (merge_per_split * S + 2.0 if S > 1 else 0.0)
+
+        best, best_t = 1, makespan(1)
+        t1 = best_t
+        for S in (2, 3, 4, 6, 8):
+            if longest / S < 8 or items * S > 6 * sms:
+                break
+            t = makespan(S)
+            if t < 0.92 * t1 and t < best_t:
+                best, best_t = S, t
+        return best
 
     def _plan_decode(self, seq_lens) -> None:
         ops.decode_plan(seq_lens, self.n_ctas, self.plan, self.min_units_per_cta)
@@ -540,11 +603,19 @@ class B200AttnBackend(AttentionBackend):
             if self.overlap_mixed != 2:
                 tail_on_side()
         if n_ext > 0 and t_ext > 0:
+            S, ws = 1, None
+            if md.kv_splits > 1 and window < 0 and not cap and layer.qk_head_dim == 128 and o3.is_contiguous():
+                S = md.kv_splits
+                need = ops.extend_split_workspace_bytes(t_ext, layer.tp_q_head_num, 128, S)
+                if self._split_ws is None or self._split_ws.numel() < need:
+                    self._split_ws = torch.empty(need, dtype=torch.uint8, device=q.device)
+                ws = self._split_ws
             ops.extend(q3[:t_ext], o3[:t_ext], pool.k_buffer[lid], pool.v_buffer[lid], table,
                        forward_batch.req_pool_indices[:n_ext], forward_batch.seq_lens[:n_ext],
                        forward_batch.extend_seq_lens[:n_ext], forward_batch.extend_prefix_lens[:n_ext],
                        md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling, cap, k_scale, v_scale,
-                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window, page_size=self.page_size)
+                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window, page_size=self.page_size,
+                       kv_splits=S, workspace=ws)
         if side is not None:
             if self.overlap_mixed == 2:  # prefill rows launched first, the tail fills the SMs they leave
                 tail_on_side()

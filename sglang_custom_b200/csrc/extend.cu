@@ -19,7 +19,8 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
                        const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D,
                        int q_dtype, int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
                        int causal, int impl, float* lse_out, int window, const uint8_t* custom_mask,
-                       const int64_t* mask_indptr, int skip_prefix_mask, int page_size, b200attn_stream_t stream) {
+                       const int64_t* mask_indptr, int skip_prefix_mask, int page_size, b200attn_stream_t stream,
+                       int kv_splits = 1, int64_t split_out_stride = 0, int64_t split_lse_stride = 0) {
   B2_REQUIRE(page_size >= 1, B200ATTN_ERR_INVALID, "extend: page_size=%d", page_size);
   B2_REQUIRE(bs >= 0 && Hq > 0 && Hkv > 0 && max_extend_len >= 0, B200ATTN_ERR_INVALID,
              "extend: bad sizes bs=%d Hq=%d Hkv=%d max_extend_len=%d", bs, Hq, Hkv, max_extend_len);
@@ -58,6 +59,7 @@ static int extend_impl(const void* q, int64_t q_tok_stride, void* out, int64_t o
   p.v_scale = v_scale;
   p.window = window; p.custom_mask = custom_mask; p.mask_indptr = mask_indptr; p.skip_prefix_mask = skip_prefix_mask;
   p.page_size = page_size;
+  p.kv_splits = kv_splits; p.split_out_stride = split_out_stride; p.split_lse_stride = split_lse_stride;
   {
     // dev knobs, read once: the exp2 split of the tcgen05 kernel and the phase-timing buffer of its kProf variant
     static const int emu = [] { const char* e = getenv("B200ATTN_EXP_EMU"); return e ? atoi(e) : 0; }();
@@ -154,3 +156,43 @@ extern "C" B2_EXPORT int b200attn_extend_paged(
                      k_scale, v_scale, causal, impl, lse_out, sliding_window_size, custom_mask,
                      mask_indptr, skip_prefix_custom_mask, page_size, stream);
 }
+
+// KV splits of the tcgen05 kernel + n-way LSE merge (see include/b200attn.h)
+extern "C" B2_EXPORT size_t b200attn_extend_split_workspace_bytes(int T, int Hq, int D, int kv_splits) {
+  if (T <= 0 || Hq <= 0 || D <= 0 || kv_splits <= 1) return 0;
+  const size_t rows = static_cast<size_t>(T) * Hq;
+  return static_cast<size_t>(kv_splits) * rows * (static_cast<size_t>(D) * 2 + sizeof(float));
+}
+
+extern "C" B2_EXPORT int b200attn_extend_split(
+    const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool, const void* v_pool,
+    int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+    const void* seq_lens, int idx_is_i64, const int32_t* extend_seq_lens, const int32_t* extend_prefix_lens,
+    const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv, int D, int q_dtype, int kv_dtype,
+    float sm_scale, float k_scale, float v_scale, int causal, float* lse_out, int page_size, int T, int kv_splits,
+    void* workspace, size_t workspace_bytes, b200attn_stream_t stream) {
+  B2_REQUIRE(kv_splits >= 1 && kv_splits <= 64, B200ATTN_ERR_INVALID, "extend_split: kv_splits=%d", kv_splits);
+  if (kv_splits == 1)
+    return extend_impl(q, q_tok_stride, out, out_tok_stride, k_pool, v_pool, pool_tok_stride, req_to_token,
+                       table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens, extend_prefix_lens,
+                       extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype, sm_scale, 0.f, k_scale,
+                       v_scale, causal, B200ATTN_EXTEND_AUTO, lse_out, -1, nullptr, nullptr, 1, page_size, stream);
+  if (bs == 0 || max_extend_len == 0 || T == 0) return B200ATTN_OK;
+  B2_REQUIRE(T > 0 && D == 128, B200ATTN_ERR_UNSUPPORTED, "extend_split: T=%d D=%d (the tcgen05 kernel needs D == 128)", T, D);
+  B2_REQUIRE(workspace != nullptr && aligned16(workspace) &&
+                 workspace_bytes >= b200attn_extend_split_workspace_bytes(T, Hq, D, kv_splits),
+             B200ATTN_ERR_WORKSPACE, "extend_split: workspace %zu < %zu bytes", workspace_bytes,
+             b200attn_extend_split_workspace_bytes(T, Hq, D, kv_splits));
+  const int64_t so = static_cast<int64_t>(T) * Hq * D, sl = static_cast<int64_t>(T) * Hq;
+  float* ws_lse = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + static_cast<size_t>(kv_splits) * so * 2);
+  // stage 1: the partials, written where `out` / `lse_out` would go (token stride Hq * D)
+  const int rc = extend_impl(q, q_tok_stride, workspace, static_cast<int64_t>(Hq) * D, k_pool, v_pool, pool_tok_stride,
+                             req_to_token, table_stride, req_pool_indices, seq_lens, idx_is_i64, extend_seq_lens,
+                             extend_prefix_lens, extend_start_loc, bs, max_extend_len, Hq, Hkv, D, q_dtype, kv_dtype,
+                             sm_scale, 0.f, k_scale, v_scale, causal, B200ATTN_EXTEND_TCGEN05, ws_lse, -1, nullptr, nullptr,
+                             1, page_size, stream, kv_splits, so, sl);
+  if (rc != B200ATTN_OK) return rc;
+  return extend_split_merge_launch(workspace, ws_lse, kv_splits, so, sl, T, Hq, D, q_dtype == B200ATTN_BF16, out,
+                                   out_tok_stride, lse_out, static_cast<cudaStream_t>(stream));
+}
+

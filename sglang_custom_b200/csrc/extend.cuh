@@ -38,6 +38,10 @@ struct ExtendParams {
   const int64_t* mask_indptr;
   int skip_prefix_mask;
   int page_size;  // allocator page size (b200attn_extend_paged); % 16 == 0 with a 16-bit pool: bulk-tensor (TMA) K/V loads
+  // KV splits of the tcgen05 kernel (b200attn_extend_split): out / lse_out then point at the partial buffers
+  // [split][token][Hq][D] (q dtype) and [split][token][Hq] (fp32), the strides are in elements
+  int kv_splits;
+  int64_t split_out_stride, split_lse_stride;
   int exp_emu;  // tcgen05 kernel: of every 4 element pairs, this many take the FMA-pipe exp2 (B200ATTN_EXP_EMU, default 0: measured best at C3)
 };
 
@@ -49,5 +53,9 @@ int extend_mma_masked_launch(const ExtendParams& p, int D, int kvb, bool q_bf16,
 // tcgen05 / TMEM kernel (extend_tc.cu): D == 128, 16-bit or FP8-E4M3 KV, logit_cap == 0
 bool extend_tc_supported(const ExtendParams& p, int D, int kvb);
 int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t st);
+// LSE merge of the kv_splits partials written by the tcgen05 kernel into the caller's out / lse_out
+int extend_split_merge_launch(const void* ws_o, const float* ws_lse, int kv_splits, int64_t split_out_stride,
+                              int64_t split_lse_stride, int T, int Hq, int D, bool bf16, void* out, int64_t out_tok_stride,
+                              float* lse_out, cudaStream_t st);
 
 }  // namespace b200attn

@@ -206,7 +206,13 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_consta
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   Prof<kProf> prof;
-  const int req = p.grid_order ? blockIdx.z : blockIdx.y;
+  // KV splits (p.kv_splits > 1, b200attn_extend_split): the request dimension of the grid carries (request, split); a
+  // CTA walks only its share of the item's K/V tiles and writes a normalised partial + LSE (merged by
+  // extend_split_merge_kernel).  Few long rows -- chunked prefill over a long prefix, head-partitioned ranks --
+  // otherwise leave most SMs idle: the grid has one CTA per (request, head pair, 128 q rows).
+  const int S = p.kv_splits;
+  const int zr = p.grid_order ? blockIdx.z : blockIdx.y;
+  const int req = zr / S, split = zr - req * S;
   const int E = p.extend_seq_lens[req];
   // heavy (late) tiles first
   const int zt = p.grid_order ? static_cast<int>(gridDim.y) - 1 - static_cast<int>(blockIdx.y)
@@ -237,8 +243,31 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_consta
   }
   nt[0] = (kv_end[0] - kv_base + kTile - 1) / kTile;
   nt[1] = valid1 ? (kv_end[1] - kv_base + kTile - 1) / kTile : 0;
-  const int n = max(nt[0], nt[1]);
-  const int kv_len = max(kv_end[0], kv_end[1]);
+  int n = max(nt[0], nt[1]);
+  int kv_len = max(kv_end[0], kv_end[1]);
+  int64_t out_off = 0, lse_off = 0;  // partial buffers of this split
+  if (S > 1) {
+    const int j_lo = split * n / S, j_hi = (split + 1) * n / S;  // this split's tiles of the item (CTA-uniform)
+    const int hi_key = kv_base + j_hi * kTile;
+    kv_base += j_lo * kTile;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      nt[t] = max(0, min(nt[t], j_hi) - j_lo);
+      kv_end[t] = min(kv_end[t], hi_key);
+    }
+    n = max(nt[0], nt[1]);
+    kv_len = max(kv_end[0], kv_end[1]);
+    out_off = static_cast<int64_t>(split) * p.split_out_stride;
+    lse_off = static_cast<int64_t>(split) * p.split_lse_stride;
+    if (n == 0) {  // fewer tiles than splits: this split is empty for every row (CTA-uniform, before any barrier)
+      if (tid < 2 * kTile) {
+        const int t = tid >> 7, row = tid & (kTile - 1);
+        if ((t == 0 || valid1) && q0[t] + row < E)
+          p.lse_out[lse_off + static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] = -INFINITY;
+      }
+      return;
+    }
+  }
 
   // ---------------------------------------------------------------- setup
   if (warp == 8) ptx::tmem_alloc<512>(tmem_slot);
@@ -309,6 +338,9 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_consta
       const int lim_row0 = p.causal ? min(P + q0[t] + 1, L) : L;                     // the tile's smallest limit
       float m_used = 0.f, l = 0.f;
       const int my_n = nt[t];
+      if (my_n == 0) {  // (splits only) this Q tile has no key in this split's range: empty partial, no MMA will arrive
+        if (row_valid) p.lse_out[lse_off + static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] = -INFINITY;
+      } else {
       const int n_unmasked = min(my_n, (lim_row0 - kv_base) / kTile);  // tiles every row of this Q tile sees completely
       const uint32_t bar_s = bar(S_FULL + t), bar_p = bar(P_FULL + 2 * t);
       // window: prefix keys below lo are invisible to this row (new-token keys, >= P, have no lower bound); the
@@ -343,7 +375,7 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_consta
       ptx::tc_fence_after();
       prof.mark(5);
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
-      uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) +
+      uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + out_off +
                       static_cast<int64_t>(start + q0[t] + row) * p.out_tok_stride + static_cast<int64_t>(head[t]) * kTile;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -363,11 +395,12 @@ extend_tc_kernel(const ExtendParams p, const int pair_heads, const __grid_consta
         }
       }
       if (p.lse_out != nullptr && row_valid)
-        p.lse_out[static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] =
+        p.lse_out[lse_off + static_cast<int64_t>(start + q0[t] + row) * p.Hq + head[t]] =
             l > 0.f ? (m_used + log2f(l)) * kLn2 : -INFINITY;
       prof.mark(6);
       prof.flush(p.prof, warp, lane);
       ptx::tc_fence_before();
+      }
     }
   } else if (warp == 8) {
     ptx::setmaxnreg_dec<kRegsOther>();
@@ -739,7 +772,8 @@ int extend_tc_launch(const ExtendParams& p, bool q_bf16, int kvb, cudaStream_t s
   const int pair_heads = (p.G % 2 == 0) ? 1 : 0;
   const int q_tiles = (p.max_extend_len + tc::kTile - 1) / tc::kTile;
   const int nz = pair_heads ? q_tiles : (q_tiles + 1) / 2;
-  dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.grid_order ? nz : p.bs, p.grid_order ? p.bs : nz);
+  const int zs = p.bs * p.kv_splits;  // (request, KV split)
+  dim3 grid(pair_heads ? p.Hq / 2 : p.Hq, p.grid_order ? nz : zs, p.grid_order ? zs : nz);
   B2_REQUIRE(grid.y <= 65535 && grid.z <= 65535, B200ATTN_ERR_UNSUPPORTED, "extend: batch %d or %d q tiles exceed the grid",
              p.bs, q_tiles);
   kern<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(p, pair_heads, maps);

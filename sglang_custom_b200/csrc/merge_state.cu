@@ -4,6 +4,7 @@
 // pure-torch statement sgl-kernel/tests/test_merge_state_v2.py:100-133.
 // HBM-bound elementwise pass: 16-byte loads, one thread per 16 bytes of a (token, head) row.
 #include "common.cuh"
+#include "extend.cuh"
 
 namespace b200attn {
 
@@ -67,6 +68,66 @@ __global__ void __launch_bounds__(256) merge_state_kernel(const T* a, const floa
     reinterpret_cast<uint4*>(out)[i] = vo;
     if (out_lse != nullptr && c == 0) out_lse[r] = se > 0.f ? logf(se) + m : -INFINITY;
   }
+}
+
+
+// n-way LSE merge of the partials the tcgen05 extend kernel writes with kv_splits > 1 (b200attn_extend_split):
+// out[t, h, :] = sum_s w_s o_s[t, h, :] / sum_s w_s,  w_s = exp(lse_s[t, h] - max_s lse_s[t, h]);  a split that saw no key
+// has lse = -inf and its (unwritten) values are never read.  One thread per 16 bytes of a (token, head) row.
+template <typename T>
+__global__ void __launch_bounds__(256)
+extend_split_merge_kernel(const T* __restrict__ ws_o, const float* __restrict__ ws_lse, int S, int64_t so, int64_t sl,
+                          int64_t rows /* T * Hq */, int Hq, int D, T* __restrict__ out, int64_t out_tok_stride,
+                          float* __restrict__ lse_out) {
+  using V = Vec16<T>;
+  const int vecs = D / V::N;
+  const int64_t total = rows * vecs;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / vecs;
+    const int c = static_cast<int>(i % vecs);
+    float m = -INFINITY;
+    for (int s = 0; s < S; ++s) m = fmaxf(m, ws_lse[s * sl + r]);
+    float acc[V::N];
+#pragma unroll
+    for (int e = 0; e < V::N; ++e) acc[e] = 0.f;
+    float se = 0.f;
+    for (int s = 0; s < S; ++s) {
+      const float l = ws_lse[s * sl + r];
+      if (l == -INFINITY) continue;
+      const float w = expf(l - m);
+      se += w;
+      const uint4 v = *reinterpret_cast<const uint4*>(ws_o + s * so + r * D + c * V::N);
+#pragma unroll
+      for (int e = 0; e < V::N; ++e) acc[e] += w * V::get(v, e);
+    }
+    const float inv = se > 0.f ? 1.f / se : 0.f;
+    uint4 vo;
+#pragma unroll
+    for (int e = 0; e < V::N; e += 2) V::set(vo, e, acc[e] * inv, acc[e + 1] * inv);
+    const int64_t tok = r / Hq, h = r % Hq;
+    *reinterpret_cast<uint4*>(out + tok * out_tok_stride + h * D + c * V::N) = vo;
+    if (lse_out != nullptr && c == 0) lse_out[r] = se > 0.f ? m + logf(se) : -INFINITY;
+  }
+}
+
+int extend_split_merge_launch(const void* ws_o, const float* ws_lse, int kv_splits, int64_t split_out_stride,
+                              int64_t split_lse_stride, int T, int Hq, int D, bool bf16, void* out, int64_t out_tok_stride,
+                              float* lse_out, cudaStream_t st) {
+  const int64_t rows = static_cast<int64_t>(T) * Hq;
+  const int64_t total = rows * (D / 8);
+  const int blocks = static_cast<int>(total < 148 * 8 * 256 ? (total + 255) / 256 : 148 * 8);
+  if (blocks == 0) return B200ATTN_OK;
+  if (bf16)
+    extend_split_merge_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
+        reinterpret_cast<const __nv_bfloat16*>(ws_o), ws_lse, kv_splits, split_out_stride, split_lse_stride, rows, Hq, D,
+        reinterpret_cast<__nv_bfloat16*>(out), out_tok_stride, lse_out);
+  else
+    extend_split_merge_kernel<__half><<<blocks, 256, 0, st>>>(
+        reinterpret_cast<const __half*>(ws_o), ws_lse, kv_splits, split_out_stride, split_lse_stride, rows, Hq, D,
+        reinterpret_cast<__half*>(out), out_tok_stride, lse_out);
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
 }
 
 }  // namespace b200attn

@@ -291,6 +291,10 @@ def merge_state(a: torch.Tensor, lse_a: torch.Tensor, b: torch.Tensor, lse_b: to
     return out, out_lse
 
 
+def extend_split_workspace_bytes(T: int, Hq: int, D: int, kv_splits: int) -> int:
+    return int(_lib.load().b200attn_extend_split_workspace_bytes(int(T), int(Hq), int(D), int(kv_splits)))
+
+
 def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
            req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
            extend_seq_lens: torch.Tensor, extend_prefix_lens: torch.Tensor, extend_start_loc: torch.Tensor,
@@ -298,7 +302,8 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
            v_scale: float = 1.0, causal: bool = True, kv_dtype: Optional[torch.dtype] = None,
            impl: int = _lib.EXTEND_AUTO, lse_out: Optional[torch.Tensor] = None, sliding_window_size: int = -1,
            custom_mask: Optional[torch.Tensor] = None, mask_indptr: Optional[torch.Tensor] = None,
-           skip_prefix_custom_mask: bool = True, page_size: int = 1) -> torch.Tensor:
+           skip_prefix_custom_mask: bool = True, page_size: int = 1, kv_splits: int = 1,
+           workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q,out [T,Hq,D]; see b200attn_extend / b200attn_extend_masked / b200attn_extend_paged in include/b200attn.h.
     page_size > 1: the allocator's page size (16-bit pools with page_size % 16 == 0 take TMA box loads).
     sliding_window_size / custom_mask / mask_indptr / skip_prefix_custom_mask carry the meaning they have in
@@ -321,6 +326,23 @@ def extend(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
     if req_pool_indices.dtype != seq_lens.dtype:
         raise B200AttnError("extend: req_pool_indices and seq_lens must share a dtype")
     masked = custom_mask is not None or (sliding_window_size is not None and sliding_window_size > -1)
+    if kv_splits > 1:
+        # K/V range of every item cut into kv_splits shares (b200attn_extend_split); workspace: uint8 / any dtype tensor of
+        # at least extend_split_workspace_bytes(T, Hq, D, kv_splits) bytes
+        if masked or (logit_cap or 0.0) != 0.0:
+            raise B200AttnError("extend: kv_splits > 1 takes plain batches only (no window, mask or logit cap)")
+        need = extend_split_workspace_bytes(T, Hq, D, kv_splits)
+        if workspace is None or not workspace.is_cuda or workspace.numel() * workspace.element_size() < need:
+            raise B200AttnError(f"extend: kv_splits={kv_splits} needs a CUDA workspace of {need} bytes")
+        check(_lib.load().b200attn_extend_split(
+            q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+            k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+            seq_lens.data_ptr(), _is_i64(seq_lens), extend_seq_lens.data_ptr(), extend_prefix_lens.data_ptr(),
+            extend_start_loc.data_ptr(), bs, int(max_extend_len), Hq, Hkv, D, _dt(q.dtype),
+            _pool_dtype(k_pool, kv_dtype), float(sm_scale), float(k_scale), float(v_scale), int(bool(causal)),
+            _ptr(lse_out), int(page_size), int(T), int(kv_splits), workspace.data_ptr(),
+            workspace.numel() * workspace.element_size(), _stream(q)), "b200attn_extend_split")
+        return out
     if masked or page_size > 1:
         if custom_mask is not None:
             _cuda(custom_mask, mask_indptr)

@@ -68,11 +68,11 @@ def test_library_targets_sm100a_and_uses_blackwell_instructions(lib):
 
 def test_version_and_error_string(lib):
     from sglang_custom_b200 import _lib
-    assert lib.b200attn_version() == 210
+    assert lib.b200attn_version() == 220
     assert isinstance(lib.b200attn_last_error(), bytes)
     assert lib.b200attn_decode_plan_bytes(256, 148) == 4 * (8 + 257 + 148)
     assert lib.b200attn_decode_workspace_bytes(148, 32, 128) == 2 * 148 * 32 * 129 * 4
-    assert _lib.version() == 210
+    assert _lib.version() == 220
 
 
 def test_argument_validation_returns_error_codes_without_a_device(lib):

@@ -265,3 +265,72 @@ def test_extend_paged_tile_loads_match_row_gathers(bs, Hq, Hkv, lens, ext, page,
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), "TMA boxes vs row gathers"
     if window < 0:
         H.assert_close(outs[0][0], H.oracle_extend(case, kp, vp), what="paged extend vs torch_native")
+
+
+SPLIT_CASES = [
+    # bs, Hq, Hkv, seq_lens, extend_lens, kwargs, kv_splits
+    (1, 8, 1, [4096 + 300], [300], {}, 4),                                   # chunked prefill over a long prefix, one KV head
+    (2, 32, 8, [3000, 700], [700, 129], {}, 2),                               # ragged; the second row has fewer tiles than rows
+    (3, 16, 4, [400, 130, 200], [300, 130, 1], {}, 4),                        # more splits than tiles for some items (empty splits)
+    (2, 28, 4, [2500, 1025], [1500, 1025], {}, 3),                            # G = 7: two consecutive q tiles per CTA
+    (2, 8, 1, [2048 + 512, 640], [512, 128], {"fp8": True, "kv_scale": 0.1135}, 3),
+    (2, 16, 2, [16 * 100 + 256, 16 * 3 + 256], [256, 256], {"page_size": 16}, 2),  # TMA page loads
+    (1, 8, 2, [1500], [1500], {"dtype": torch.float16}, 8),
+]
+
+
+@pytest.mark.parametrize("bs,Hq,Hkv,lens,ext,kw,S", SPLIT_CASES)
+def test_extend_kv_splits_match_unsplit_and_oracle(bs, Hq, Hkv, lens, ext, kw, S, device):
+    """b200attn_extend_split: every item's K/V range cut into S shares (separate CTAs), partials merged by LSE.  The
+    partials are rounded to the q dtype, so the result is compared with the unsplit tcgen05 kernel and with the oracle
+    inside the parity bound (not bit for bit); the LSE must agree too."""
+    case = synth.make_case(bs, Hq, Hkv, 128, lens, extend_lens=ext, seed=977 + S + Hq, **kw)
+    kp, vp = H.pool_after_write(case)
+    want = H.oracle_extend(case, kp, vp)
+    base, lse0 = _direct(case, device, kp, vp, _lib.EXTEND_TCGEN05, want_lse=True)
+    c = H.to_device(case, device)
+    s = case.kv_scale if case.fp8 else 1.0
+    ws = torch.full((ops.extend_split_workspace_bytes(case.T, Hq, 128, S),), 0xFF, dtype=torch.uint8, device=device)  # NaN-filled
+    out = torch.empty_like(c.q)
+    lse = torch.empty((case.T, Hq), dtype=torch.float32, device=device)
+    ops.extend(c.q, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens,
+               c.extend_seq_lens, c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale,
+               k_scale=s, v_scale=s, kv_dtype=torch.float8_e4m3fn if case.fp8 else None, lse_out=lse,
+               page_size=kw.get("page_size", 1), kv_splits=S, workspace=ws)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all(), "an empty split's (unwritten) partial leaked into the merge"
+    H.assert_close(out, want, what=f"kv_splits={S} vs torch_native")
+    H.assert_close(out, base.cpu(), 4e-3, 4e-4, what=f"kv_splits={S} vs the unsplit kernel")
+    assert torch.allclose(lse, lse0, atol=2e-3, rtol=1e-4)
+
+
+def test_extend_split_rejects_bad_arguments(device):
+    case = synth.make_case(1, 8, 1, 128, [512], extend_lens=[256], seed=5)
+    kp, vp = H.pool_after_write(case)
+    c = H.to_device(case, device)
+    out = torch.empty_like(c.q)
+    args = (c.q, out, kp.to(device), vp.to(device), c.req_to_token, c.req_pool_indices, c.seq_lens, c.extend_seq_lens,
+            c.extend_prefix_lens, c.extend_start_loc, case.max_extend_len, case.sm_scale)
+    with pytest.raises(ops.B200AttnError):  # no workspace
+        ops.extend(*args, kv_splits=2)
+    small = torch.empty(16, dtype=torch.uint8, device=device)
+    with pytest.raises(ops.B200AttnError):  # workspace too small
+        ops.extend(*args, kv_splits=2, workspace=small)
+    ws = torch.empty(ops.extend_split_workspace_bytes(case.T, 8, 128, 2), dtype=torch.uint8, device=device)
+    with pytest.raises(ops.B200AttnError):  # plain batches only
+        ops.extend(*args, kv_splits=2, workspace=ws, sliding_window_size=64)
+
+
+def test_backend_picks_kv_splits_for_a_long_prefix_chunk(device):
+    """Chunked prefill of one request over a long prefix with one KV head per rank: 4 x 2 items for 148 SMs.  The backend
+    must choose a split factor from the host-side length lists (no sync) and still match the oracle."""
+    case = synth.make_case(1, 8, 1, 128, [6000 + 256], extend_lens=[256], seed=31)
+    kp, vp = H.pool_after_write(case)
+    r = H.Runner(case, device)
+    out = r.forward()
+    assert r.backend.forward_metadata.kv_splits > 1
+    H.assert_close(out, H.oracle_extend(case, kp, vp), what="backend with KV splits")
+    r.backend.extend_kv_splits = 1
+    out1 = r.forward()
+    assert r.backend.forward_metadata.kv_splits == 1
+    H.assert_close(out, out1, 4e-3, 4e-4, what="split vs unsplit through the backend")

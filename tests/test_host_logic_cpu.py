@@ -175,3 +175,31 @@ def test_tp_gloo_head_sharded_generation_and_global_subcase(world):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert same and ok and (hq, hkv) == (8, 2) and all_ok is False
+
+
+def test_choose_kv_splits_cost_model():
+    """The backend's split factor for prefill rows (host-side launch simulation, backend._choose_kv_splits): big grids
+    are never split, a long-prefix chunk on few heads is, and the answer is a pure function of the host length lists."""
+    from sglang_custom_b200 import synth
+    from sglang_custom_b200.backend import B200AttnBackend
+
+    class Stub:
+        extend_kv_splits = 0
+        n_ctas = 148
+
+    def choose(Hq, Hkv, ext, pre):
+        s = Stub()
+        s.num_head, s.num_kv_head = Hq, Hkv
+        return B200AttnBackend._choose_kv_splits(s, ext, pre)
+
+    assert choose(32, 8, [2048] * 16, [2048] * 16) == 1        # config 3: 4096 items
+    assert choose(32, 8, [300] * 3, [100] * 3) == 1            # short rows
+    assert choose(8, 1, [2048], [30000]) > 1                   # one long chunked-prefill row, one KV head per rank
+    assert choose(8, 1, [1024] * 2, [8192] * 2) > 1
+    lens, ext, n_ext = synth.c5_lengths()
+    pre = [l - e for l, e in zip(lens[:n_ext], ext[:n_ext])]
+    assert choose(64, 8, ext[:n_ext], pre) == 1                # config 5 on one GPU: 2048 items
+    assert choose(8, 1, ext[:n_ext], pre) > 1                  # config 5 at TP 8: 256 skewed items
+    s = Stub()
+    s.num_head, s.num_kv_head, s.extend_kv_splits = 8, 1, 4
+    assert B200AttnBackend._choose_kv_splits(s, [128], [0]) == 4  # forced
