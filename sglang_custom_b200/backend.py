@@ -77,6 +77,8 @@ class ForwardMetadata:
     n_extend_tokens: int = -1
     # KV splits of the prefill rows' extend kernel (chosen on the host from extend_*_lens_cpu, see _choose_kv_splits)
     kv_splits: int = 1
+    # prefill rows re-ordered longest first: permuted copies of the per-request arrays (None: batch order)
+    ext_order: Optional[dict] = None
     # TARGET_VERIFY (speculative decoding): every request contributes num_draft_tokens query rows over its
     # seq_lens cached tokens; built on the device, no host sync (triton_backend.py:227-264)
     extend_seq_lens: Optional[torch.Tensor] = None
@@ -135,6 +137,7 @@ class B200AttnBackend(AttentionBackend):
         # prefill rows: 0 = choose KV splits per batch (_choose_kv_splits), 1 = never, n = always n
         self.extend_kv_splits = int(os.environ.get("B200ATTN_EXTEND_KV_SPLITS", "0"))
         self._split_ws = None
+        self.sort_extend_requests = os.environ.get("B200ATTN_SORT_EXTEND", "1") != "0"  # prefill rows: longest request first
         self.verify_via_decode = True  # TARGET_VERIFY: cached-prefix part on the split-KV decode kernel
         # ... as long as it takes at most this many passes of 16 (draft token, q head) rows: a pass streams the prefix once
         # (0.65 ms at bs 256 / ctx 4096, profiles/r01_time_masked_verify.txt), the masked extend kernel alone takes 6.9 ms
@@ -211,12 +214,30 @@ class B200AttnBackend(AttentionBackend):
         if n_tail:
             # a query with extend_len 1 at position L-1 sees all L keys: exactly a decode row
             self._plan_decode(forward_batch.seq_lens[bs - n_tail:])
-        kv_splits = 1
+        kv_splits, ext_order = 1, None
         pre_cpu = getattr(forward_batch, "extend_prefix_lens_cpu", None)
-        if ext_cpu is not None and pre_cpu is not None and self.extend_kv_splits != 1:
-            kv_splits = self._choose_kv_splits(ext_cpu[:len(ext_cpu) - n_tail], list(pre_cpu)[:len(ext_cpu) - n_tail])
+        if ext_cpu is not None and pre_cpu is not None:
+            n_ext = len(ext_cpu) - n_tail
+            head_ext, head_pre = ext_cpu[:n_ext], list(pre_cpu)[:n_ext]
+            # Longest request first: the extend grid is a queue in block-index order (request slowest), and a long row
+            # that starts last is the tail of the launch.  The kernels address q / out rows through extend_start_loc,
+            # so permuting the per-request arrays is all it takes; results are unchanged bit for bit.
+            if self.sort_extend_requests and n_ext > 1:
+                order = sorted(range(n_ext), key=lambda i: -(head_pre[i] + head_ext[i]))
+                if order != list(range(n_ext)):
+                    idx = torch.tensor(order, dtype=torch.int64, device=forward_batch.seq_lens.device)
+                    ext_order = dict(
+                        req_pool_indices=forward_batch.req_pool_indices[:n_ext][idx],
+                        seq_lens=forward_batch.seq_lens[:n_ext][idx],
+                        extend_seq_lens=forward_batch.extend_seq_lens[:n_ext][idx],
+                        extend_prefix_lens=forward_batch.extend_prefix_lens[:n_ext][idx],
+                        extend_start_loc=start[:n_ext][idx])
+                    head_ext, head_pre = [head_ext[i] for i in order], [head_pre[i] for i in order]
+            if self.extend_kv_splits != 1:
+                kv_splits = self._choose_kv_splits(head_ext, head_pre)
         self.forward_metadata = ForwardMetadata(False, bs, extend_start_loc=start, max_extend_len=max_extend,
-                                                n_decode_tail=n_tail, n_extend_tokens=t_ext, kv_splits=kv_splits)
+                                                n_decode_tail=n_tail, n_extend_tokens=t_ext, kv_splits=kv_splits,
+                                                ext_order=ext_order)
 
     def _choose_kv_splits(self, ext, pre) -> int:
         """How many shares the K/V range of every prefill item is cut into (b200attn_extend_split).  The tcgen05 extend
@@ -610,12 +631,15 @@ class B200AttnBackend(AttentionBackend):
                 if self._split_ws is None or self._split_ws.numel() < need:
                     self._split_ws = torch.empty(need, dtype=torch.uint8, device=q.device)
                 ws = self._split_ws
+            eo = md.ext_order
             ops.extend(q3[:t_ext], o3[:t_ext], pool.k_buffer[lid], pool.v_buffer[lid], table,
-                       forward_batch.req_pool_indices[:n_ext], forward_batch.seq_lens[:n_ext],
-                       forward_batch.extend_seq_lens[:n_ext], forward_batch.extend_prefix_lens[:n_ext],
-                       md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling, cap, k_scale, v_scale,
-                       causal=causal, kv_dtype=pool.dtype, sliding_window_size=window, page_size=self.page_size,
-                       kv_splits=S, workspace=ws)
+                       eo["req_pool_indices"] if eo else forward_batch.req_pool_indices[:n_ext],
+                       eo["seq_lens"] if eo else forward_batch.seq_lens[:n_ext],
+                       eo["extend_seq_lens"] if eo else forward_batch.extend_seq_lens[:n_ext],
+                       eo["extend_prefix_lens"] if eo else forward_batch.extend_prefix_lens[:n_ext],
+                       eo["extend_start_loc"] if eo else md.extend_start_loc[:n_ext], md.max_extend_len, layer.scaling,
+                       cap, k_scale, v_scale, causal=causal, kv_dtype=pool.dtype, sliding_window_size=window,
+                       page_size=self.page_size, kv_splits=S, workspace=ws)
         if side is not None:
             if self.overlap_mixed == 2:  # prefill rows launched first, the tail fills the SMs they leave
                 tail_on_side()

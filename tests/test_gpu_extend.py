@@ -334,3 +334,24 @@ def test_backend_picks_kv_splits_for_a_long_prefix_chunk(device):
     out1 = r.forward()
     assert r.backend.forward_metadata.kv_splits == 1
     H.assert_close(out, out1, 4e-3, 4e-4, what="split vs unsplit through the backend")
+
+
+def test_backend_longest_request_first_is_bit_identical(device):
+    """The backend launches the prefill rows longest request first (permuted per-request arrays; q / out rows are addressed
+    through extend_start_loc): same bits as batch order, including a MIXED batch with a decode tail behind the rows."""
+    for lens, ext, mode in (([300, 2600, 129, 1400], [200, 600, 129, 700], None),
+                            ([260, 1900, 700, 45, 333], [130, 900, 1, 1, 1], "MIXED")):
+        case = synth.make_case(len(lens), 16, 4, 128, lens, extend_lens=ext, seed=61)
+        kp, vp = H.pool_after_write(case)
+        r = H.Runner(case, device)
+        r.backend.extend_kv_splits = 1
+        fm = getattr(r.itf.ForwardMode, mode) if mode else None
+        r.backend.sort_extend_requests = True
+        a = r.forward(fm).clone()
+        assert r.backend.forward_metadata.ext_order is not None
+        r.backend.sort_extend_requests = False
+        b = r.forward(fm)
+        assert r.backend.forward_metadata.ext_order is None
+        assert torch.equal(a, b)
+        want = H.oracle_extend(case, kp, vp)
+        H.assert_close(a, want, what="sorted launch vs torch_native")
