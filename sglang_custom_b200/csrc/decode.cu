@@ -1122,9 +1122,10 @@ static bool fp8_tokm_enabled() {
 }
 
 // B200ATTN_DECODE_FP8_BIG: 0 = two tile groups over 32 KiB stages (the form before round 2's last change), 1 = 64 KiB
-// stages for head blocks >= 2 (default), 2 = for every head block
+// stages for head blocks >= 2, 2 = for every head block (default; one head per CTA: 256-token tiles, +2 % at C4 / TP 8,
+// neutral at low batch)
 static int fp8_big_level() {
-  static const int lv = [] { const char* e = getenv("B200ATTN_DECODE_FP8_BIG"); return e ? atoi(e) : 1; }();
+  static const int lv = [] { const char* e = getenv("B200ATTN_DECODE_FP8_BIG"); return e ? atoi(e) : 2; }();
   return lv;
 }
 
@@ -1132,8 +1133,7 @@ template <int D, int HB, int KVB, bool kQBf16, bool kG8, bool kTma>
 static int launch_decode_t(const DecodeParams& p, int head_groups, cudaStream_t st) {
   if constexpr (KVB == 1 && kG8) {
     if (fp8_tokm_enabled()) {
-      // 64 KiB stages shared by all 16 warps (32 / 64 / 128 tokens per tile for 8 / 4 / 2 heads per CTA; one head per
-      // CTA -- 256-token tiles -- gains 2 % at C4 / TP 8 and is left to B200ATTN_DECODE_FP8_BIG=2)
+      // 64 KiB stages shared by all 16 warps (32 / 64 / 128 / 256 tokens per tile for 8 / 4 / 2 / 1 heads per CTA)
       if constexpr (D == 128) {
         if (fp8_big_level() >= (HB >= 2 ? 1 : 2))
           return launch_decode_cw<D, HB, KVB, kQBf16, kG8, 16, true, kTma, true>(p, head_groups, st);
