@@ -21,6 +21,7 @@
  *   b200attn_extend              layers/attention/torch_native_backend.py:27-110,182-224 (oracle),
  *                                triton_ops/extend_attention.py:306-438, sgl-kernel/csrc/cpu/extend.cpp:579
  *   b200attn_decode_multiq       cached-prefix part of TARGET_VERIFY batches (triton_backend.py:227-264)
+ *   b200attn_decode_static_ws    (no counterpart in the reference) decode for hosts that cannot allocate a workspace
  *   b200attn_decode_paged, b200attn_decode_multiq_paged, b200attn_extend_paged, b200attn_extend_split
  *                                the same three for paged pools (mem_cache/allocator.py:444-447 slot layout)
  *   b200attn_decode_plan_window  layers/attention/triton_backend.py:927-955 (update_sliding_window_buffer)
@@ -236,6 +237,37 @@ int b200attn_decode_multiq_paged(const void* q, int64_t q_req_stride, int64_t q_
                                  float sm_scale, float logit_cap, float k_scale, float v_scale, const int32_t* plan,
                                  int n_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
                                  int64_t lse_req_stride, int page_size, b200attn_stream_t stream);
+
+/* Decode with the split-KV workspace built into the library -- this one has NO counterpart in the reference.
+ *
+ * For hosts that can hand over the tensors of a forward pass but cannot produce one more device buffer: a cgo / JNI /
+ * ctypes binding that does not link the CUDA runtime, or a plugin inside a server (SGLang included) that has already
+ * given all free HBM to the KV pool and must not cudaMalloc in its step loop (the call can fail for lack of memory, and
+ * it stalls every stream on the device while it runs).  Everything else is b200attn_decode_paged with stage = 0:
+ * same arguments, same kernels, same results bit for bit; pass page_size = 1 for b200attn_decode's behaviour.
+ *
+ *   - The fp32 partials go into a B200ATTN_DECODE_STATIC_WS_BYTES array that is part of the library's device image.
+ *     Each GPU the library's kernels are loaded on holds that much memory until the process exits.
+ *   - Limit: b200attn_decode_workspace_bytes(n_ctas, Hq, D) must not exceed b200attn_decode_static_ws_capacity()
+ *     (10 MiB: 148 CTAs x 64 query heads x D 128 fits); larger problems return B200ATTN_ERR_WORKSPACE and the message
+ *     in b200attn_last_error() says how much was asked for.  Use fewer CTAs, or b200attn_decode with your own buffer.
+ *   - The call allocates nothing, on the host's CUDA heap or anywhere else, and frees nothing.
+ *   - The FIRST call on each device resolves the array's device address (cudaGetSymbolAddress, with that device
+ *     current -- the device `stream` belongs to must be the current one, as for every entry point here).  Make that
+ *     first call during start-up, before any stream capture begins on that device.
+ *   - All calls on a device share the one array and find the previous call's partials in it.  Nothing needs to be
+ *     zero at the start, so nothing is cleared; but two calls that can overlap on the GPU (different streams without
+ *     an event between them, or two host threads on two streams) overwrite each other's partials.  Calls on ONE
+ *     stream are ordered and safe.  b200attn_decode with separate workspaces is the way to run decodes concurrently. */
+#define B200ATTN_DECODE_STATIC_WS_BYTES (10u << 20)
+size_t b200attn_decode_static_ws_capacity(void);
+int b200attn_decode_static_ws(const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride,
+                              const void* k_pool, const void* v_pool, int64_t pool_tok_stride,
+                              const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+                              const void* seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype,
+                              int kv_dtype, float sm_scale, float logit_cap, float k_scale, float v_scale,
+                              const int32_t* plan, int n_ctas, float* lse_out, int page_size,
+                              b200attn_stream_t stream);
 
 /* ---------------------------------------------------------------- 2-way LSE merge
  * out = (e^{la-m} a + e^{lb-m} b) / (e^{la-m} + e^{lb-m}),  lse = log(sum) + m, m = max(la, lb);

@@ -48,6 +48,9 @@ SIGNATURES = {
     "b200attn_decode_multiq_paged": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i,
                                           _i, _i, _i, _i, _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _sz, _vp, _i64, _i,
                                           _vp]),
+    "b200attn_decode_static_ws_capacity": (_sz, []),
+    "b200attn_decode_static_ws": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i,
+                                       _i, _i, _f, _f, _f, _f, _vp, _i, _vp, _i, _vp]),
     "b200attn_decode_merge": (_i, [_vp, _i64, _i, _i, _i, _i, _vp, _i, _vp, _sz, _vp, _vp]),
     "b200attn_merge_state": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b200attn_extend": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp,

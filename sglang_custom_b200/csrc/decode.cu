@@ -1367,6 +1367,73 @@ extern "C" B2_EXPORT int b200attn_decode_multiq_paged(B2_MULTIQ_PARAMS, int page
   return decode_multiq_entry(page_size, B2_MULTIQ_ARGS, stream);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// b200attn_decode_static_ws: b200attn_decode / b200attn_decode_paged for callers that have no way to get device
+// memory for the split-KV partials.  No counterpart in the reference.
+//
+// Who that is: a host that binds this library from another runtime (cgo, JNI, a ctypes stub inside a server whose
+// own allocator has already claimed the GPU's memory for the KV pool) holds only the tensors it was handed -- q, out,
+// the pools, the tables.  It cannot call cudaMalloc itself: it may not link the CUDA runtime at all, the memory may
+// simply be gone (SGLang sizes the pool to fill what is free), and cudaMalloc / cudaFree stall every stream of the
+// device while they run, which a serving loop cannot afford per step.  Such a caller has nowhere to put the fp32
+// partials the split-KV kernel hands to the merge kernel.
+//
+// So the partials live in the array below, which is part of the library image: every GPU on which the library's
+// kernels get loaded carries these B200ATTN_DECODE_STATIC_WS_BYTES until the process exits, whether or not this
+// entry point is ever called.  Nothing in the array has to start at zero (stage 1 writes every slot the merge
+// reads, exactly as with a caller-provided torch.empty workspace), so nothing is cleared between calls.
+//
+// `g_decode_static_ws` in HOST code is only a handle for the runtime's symbol table, not an address a kernel could
+// use; the device address is looked up once per device with cudaGetSymbolAddress (static_ws_for_current_device).
+static __device__ __align__(256) unsigned char g_decode_static_ws[B200ATTN_DECODE_STATIC_WS_BYTES];
+
+namespace b200attn {
+
+// Device address of g_decode_static_ws on the CURRENT device; resolved on the first call per device and remembered.
+// The lookup makes the runtime load this module onto the device if it has not yet, which is why the first call on a
+// device belongs before any stream capture.
+static int static_ws_for_current_device(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* ptrs[kMaxDevices] = {};  // written once per slot; racing first calls store the same value
+  int dev = -1;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_REQUIRE(dev >= 0 && dev < kMaxDevices, B200ATTN_ERR_UNSUPPORTED, "decode_static_ws: device ordinal %d >= %d", dev,
+             kMaxDevices);
+  void* ptr = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (ptr == nullptr) {
+    B2_CUDA(cudaGetSymbolAddress(&ptr, g_decode_static_ws));
+    B2_REQUIRE(ptr != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 255u) == 0, B200ATTN_ERR_CUDA,
+               "decode_static_ws: cudaGetSymbolAddress returned %p for the static workspace", ptr);
+    __atomic_store_n(&ptrs[dev], ptr, __ATOMIC_RELEASE);
+  }
+  *out = ptr;
+  return B200ATTN_OK;
+}
+
+}  // namespace b200attn
+
+extern "C" B2_EXPORT size_t b200attn_decode_static_ws_capacity(void) { return B200ATTN_DECODE_STATIC_WS_BYTES; }
+
+extern "C" B2_EXPORT int b200attn_decode_static_ws(
+    const void* q, int64_t q_tok_stride, void* out, int64_t out_tok_stride, const void* k_pool, const void* v_pool,
+    int64_t pool_tok_stride, const int32_t* req_to_token, int64_t table_stride, const void* req_pool_indices,
+    const void* seq_lens, int idx_is_i64, int bs, int Hq, int Hkv, int D, int q_dtype, int kv_dtype, float sm_scale,
+    float logit_cap, float k_scale, float v_scale, const int32_t* plan, int n_ctas, float* lse_out, int page_size,
+    b200attn_stream_t stream) {
+  if (bs == 0) return B200ATTN_OK;
+  const size_t need = b200attn_decode_workspace_bytes(n_ctas, Hq, D);
+  B2_REQUIRE(need > 0, B200ATTN_ERR_INVALID, "decode_static_ws: bad sizes n_ctas=%d Hq=%d D=%d", n_ctas, Hq, D);
+  B2_REQUIRE(need <= static_cast<size_t>(B200ATTN_DECODE_STATIC_WS_BYTES), B200ATTN_ERR_WORKSPACE,
+             "decode_static_ws: n_ctas=%d x Hq=%d x D=%d needs %zu bytes of partials, the built-in workspace holds %zu; "
+             "use b200attn_decode with a caller-provided workspace (or fewer CTAs)",
+             n_ctas, Hq, D, need, static_cast<size_t>(B200ATTN_DECODE_STATIC_WS_BYTES));
+  void* workspace = nullptr;
+  const int rc = static_ws_for_current_device(&workspace);
+  if (rc != B200ATTN_OK) return rc;
+  const size_t workspace_bytes = B200ATTN_DECODE_STATIC_WS_BYTES;
+  return decode_entry(B2_DECODE_ARGS, page_size, true, stream);
+}
+
 #ifdef B200ATTN_DEBUG_WAIT
 // development build only: timed-out mbarrier waits recorded by the decode kernels (see tc_ptx.cuh); returns the count
 extern "C" B2_EXPORT int b200attn_debug_wait_dump(unsigned int* host_out, int clear) {

@@ -235,6 +235,49 @@ def decode(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: tor
     return out
 
 
+def decode_static_ws_capacity() -> int:
+    """Bytes of split-KV partials the library's built-in workspace can hold (b200attn_decode_static_ws_capacity)."""
+    return _lib.load().b200attn_decode_static_ws_capacity()
+
+
+def decode_static_ws(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+                     req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                     plan: torch.Tensor, n_ctas: int, sm_scale: float, logit_cap: float = 0.0,
+                     k_scale: float = 1.0, v_scale: float = 1.0, kv_dtype: Optional[torch.dtype] = None,
+                     lse_out: Optional[torch.Tensor] = None, page_size: int = 1) -> torch.Tensor:
+    """`decode(..., stage="both")` without the `workspace` argument: b200attn_decode_static_ws.
+
+    For embedders that cannot hand the library a scratch buffer -- a binding with no CUDA allocator of its own, or a
+    server that has already given all free HBM to the KV pool and must not cudaMalloc per step.  The partials go into
+    a 10 MiB array inside the library (`decode_static_ws_capacity()`); a problem whose
+    `decode_workspace_bytes(n_ctas, Hq, D)` is larger raises B200AttnError [WORKSPACE].  Neither this wrapper nor the
+    C call allocates.  Calls share that one array per GPU: keep them on one stream (or order them with events), and
+    make the first call on each GPU during start-up, before capturing any stream there."""
+    _cuda(q, out, k_pool, v_pool, req_to_token, req_pool_indices, seq_lens, plan, lse_out)
+    bs, Hq, D = q.shape
+    Hkv = k_pool.shape[1]
+    if out.shape != q.shape or out.dtype != q.dtype:
+        raise B200AttnError("decode_static_ws: out must match q")
+    if q.stride(2) != 1 or q.stride(1) != D or out.stride(2) != 1 or out.stride(1) != D:
+        raise B200AttnError("decode_static_ws: q/out head stride must be D")
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise B200AttnError("decode_static_ws: req_to_token must be int32 with contiguous rows")
+    if req_pool_indices.dtype != seq_lens.dtype:
+        raise B200AttnError("decode_static_ws: req_pool_indices and seq_lens must share a dtype")
+    if k_pool.stride(1) != D or k_pool.stride(2) != 1 or v_pool.stride() != k_pool.stride():
+        raise B200AttnError("decode_static_ws: pool must be [P,Hkv,D] with strides (*, D, 1)")
+    if lse_out is not None and (lse_out.dtype != torch.float32 or not lse_out.is_contiguous()):
+        raise B200AttnError("decode_static_ws: lse_out must be contiguous fp32 [bs,Hq]")
+    with torch.cuda.device(q.device):  # the symbol lookup and the launch both act on the current device
+        check(_lib.load().b200attn_decode_static_ws(
+            q.data_ptr(), q.stride(0), out.data_ptr(), out.stride(0), k_pool.data_ptr(), v_pool.data_ptr(),
+            k_pool.stride(0), req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+            seq_lens.data_ptr(), _is_i64(seq_lens), bs, Hq, Hkv, D, _dt(q.dtype), _pool_dtype(k_pool, kv_dtype),
+            float(sm_scale), float(logit_cap or 0.0), float(k_scale), float(v_scale), plan.data_ptr(), int(n_ctas),
+            _ptr(lse_out), int(page_size), _stream(q)), "b200attn_decode_static_ws")
+    return out
+
+
 def decode_multiq(q: torch.Tensor, out: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
                   req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
                   plan: torch.Tensor, n_ctas: int, workspace: torch.Tensor, sm_scale: float, logit_cap: float = 0.0,
