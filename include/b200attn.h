@@ -34,7 +34,7 @@
  *   - All pointers are DEVICE pointers unless the name ends in `_host`.
  *   - The library never allocates or frees device memory and never synchronises
  *     the host with the device; every kernel is enqueued on `stream`.
- *     All calls are CUDA-graph-capture safe.
+ *     All calls are CUDA-graph-capture safe (b200attn_decode_static_ws states its own rules and makes no such claim).
  *   - Return value: 0 on success, a negative B200ATTN_ERR_* code otherwise; the
  *     message is available (per thread) from b200attn_last_error().
  *   - Strides are in ELEMENTS of the tensor's own dtype unless stated.

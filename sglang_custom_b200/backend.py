@@ -147,9 +147,11 @@ class B200AttnBackend(AttentionBackend):
         self.overlap_mixed = 2
         self._side_stream = None
         self.route_decode_tail = True  # MIXED batches: extend_len == 1 tail rows go to the decode kernel
-        # (layer_id, id(forward_batch)) of the last fused RoPE + KV write (rotary.forward_fused_kv): the only case in
-        # which forward_* may be called with k/v and save_kv_cache=False (see _require_kv_in_pool)
+        # (layer_id, sequence number) of the last fused RoPE + KV write (rotary.forward_fused_kv), also stamped on the
+        # batch object it was done for: the only case in which forward_* may be called with k/v and
+        # save_kv_cache=False (see _require_kv_in_pool)
         self._kv_written = None
+        self._kv_written_seq = 0
         self.check_loc = os.environ.get("B200ATTN_CHECK_LOC", "0") not in ("", "0")
 
     # ------------------------------------------------------------------ buffers
@@ -183,6 +185,11 @@ class B200AttnBackend(AttentionBackend):
                                                                     forward_batch.seq_lens, spec_info, None)
                 return
             if mode.is_decode_or_idle():
+                if bs == 0 or (hasattr(mode, "is_idle") and mode.is_idle()):
+                    # an idle batch that carries an idle EagleDraftInput / EagleVerifyInput (EAGLE with DP attention):
+                    # the reference reads spec_info.kv_indptr and launches nothing for it
+                    self.forward_metadata = ForwardMetadata(True, 0)
+                    return
                 # a draft decode step: rows, lengths and table come from B200MultiStepDraftBackend
                 # (the reference hands kv_indptr / kv_indices over the same way, triton_backend.py:203-205)
                 self.forward_metadata = self._draft_step_metadata(spec_info)
@@ -413,6 +420,9 @@ class B200AttnBackend(AttentionBackend):
             self.forward_metadata = md
             return
         if forward_mode.is_decode_or_idle() and spec_info is not None:
+            if bs == 0 or (hasattr(forward_mode, "is_idle") and forward_mode.is_idle()):
+                self.forward_metadata = ForwardMetadata(True, 0)  # idle batch with an idle spec input: nothing to launch
+                return
             self.forward_metadata = self._draft_step_metadata(spec_info)  # fixed buffers owned by the multi-step backend
             return
         raise NotImplementedError(f"b200 attention backend: {forward_mode!r} does not run under CUDA graphs "
@@ -432,6 +442,8 @@ class B200AttnBackend(AttentionBackend):
             self._draft_extend_metadata(bs, seq_lens, spec_info, self.cg_draft_extend)
             return
         if forward_mode.is_decode_or_idle() and spec_info is not None:
+            if bs == 0 or (hasattr(forward_mode, "is_idle") and forward_mode.is_idle()):
+                return
             self._draft_step_metadata(spec_info)  # re-plans over the step's (in place refreshed) lengths
             return
         raise NotImplementedError(f"b200 attention backend: {forward_mode!r} does not run under CUDA graphs "
@@ -467,7 +479,11 @@ class B200AttnBackend(AttentionBackend):
 
     def note_kv_written(self, layer, forward_batch) -> None:
         """Called by rotary.forward_fused_kv: this layer's new K/V of this batch are already in the pool."""
-        self._kv_written = (layer.layer_id, id(forward_batch))
+        # The mark lives ON the batch object: a (layer, id(batch)) pair kept here could be satisfied by a later batch
+        # that CPython happened to give the same id after this one was collected.
+        self._kv_written_seq += 1
+        self._kv_written = (layer.layer_id, self._kv_written_seq)
+        forward_batch.b200_kv_written = (id(self),) + self._kv_written
 
     def _require_kv_in_pool(self, layer, forward_batch, k) -> None:
         """save_kv_cache=False contract.  Every key -- cached prefix and new tokens alike -- is read from the paged
@@ -476,7 +492,11 @@ class B200AttnBackend(AttentionBackend):
         radix_attention.py:91-99), or rotary.forward_fused_kv wrote them for exactly this layer and batch.  The Triton
         backend would attend over the passed k/v instead (extend_attention_fwd reads K_Extend/V_Extend); silently
         reading stale pool rows in that situation is the one thing this must never do."""
-        if k is None or self._kv_written == (layer.layer_id, id(forward_batch)):
+        if k is None:
+            return
+        mark = getattr(forward_batch, "b200_kv_written", None)
+        if mark is not None and self._kv_written is not None and mark == (id(self),) + self._kv_written \
+                and mark[1] == layer.layer_id:
             return
         raise B200AttnError(
             "save_kv_cache=False with k/v given, but the new tokens of this layer/batch were not written by "

@@ -52,10 +52,23 @@ def build_branch_table(req_to_token: torch.Tensor, req_pool_indices: torch.Tenso
     width = table.shape[1]
     start = draft_token_start(seq_lens, topk, num_steps, page_size).reshape(-1)      # [bs * topk]
     j = torch.arange(num_steps, device=table.device, dtype=torch.int64)[None, :]
-    src_pos = (start[:, None] + j).clamp_(max=width - 1)
-    dst_pos = (seq_lens.to(torch.int64).repeat_interleave(topk)[:, None] + j).clamp_(max=width - 1)
-    vals = src.repeat_interleave(topk, dim=0).gather(1, src_pos)
-    table.scatter_(1, dst_pos, vals)
+    L = seq_lens.to(torch.int64).repeat_interleave(topk)[:, None]
+    src_pos = start[:, None] + j
+    dst_pos = L + j
+    # A draft slot whose source or destination lies past the row (seq_len + num_steps > width) is dropped, the way the
+    # reference masks its out-of-range loads (eagle_utils.py:889-905) -- it is never aliased onto the last column.
+    valid = (src_pos < width) & (dst_pos < width)
+    dst_c = dst_pos.clamp(max=width - 1)
+    rows = src.repeat_interleave(topk, dim=0)
+    vals = torch.where(valid, rows.gather(1, src_pos.clamp(max=width - 1)), rows.gather(1, dst_c))
+    # Lanes past the row all land on column width - 1 after the clamp.  scatter_ with duplicate indices keeps an
+    # unspecified one, so they are given the value of the lane that really owns that column (or the column's content
+    # when none does): every duplicate writes the same number and the result is deterministic.
+    j_last = (width - 1) - L
+    owned = (j_last >= 0) & (j_last < num_steps)
+    last_val = torch.where(owned, vals.gather(1, j_last.clamp(0, num_steps - 1)), rows[:, width - 1:width])
+    vals = torch.where(dst_pos > width - 1, last_val, vals)
+    table.scatter_(1, dst_c, vals)
     return table
 
 

@@ -13,6 +13,8 @@ ATTN_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("*.pt") if not p.stem.sta
 MASKED_EXTEND_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("masked_*.pt") if "decode" not in p.stem)
 MASKED_DECODE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("masked_*decode*.pt"))
 ROPE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("rope*.pt"))
+# DRAFT_EXTEND both ways (FlashInfer-style causal, Triton-style double count): tests/golden/make_golden_draft_extend.py
+DRAFT_EXTEND_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("draft_extend_*.pt"))
 KVWRITE_FIXTURES = sorted(p.stem for p in GOLDEN_DIR.glob("kvwrite*.pt"))
 
 

@@ -50,3 +50,25 @@ def test_draft_token_start_formulas():
     # page 16: branch t starts ceil((L % 16 + steps) / 16) pages further (eagle_utils.py:875-883)
     assert draft_token_start(sl, 2, 3, 16).tolist() == [[48, 64], [17, 33], [100, 116]]
     assert draft_token_start(torch.tensor([30]), 3, 5, 16).tolist() == [[30, 62, 94]]
+
+
+@pytest.mark.parametrize("L,topk,steps,page", [(29, 2, 4, 1), (31, 3, 3, 1), (32, 2, 2, 1), (26, 2, 5, 16), (30, 4, 2, 1)])
+def test_branch_table_drops_slots_past_the_row_instead_of_aliasing_them(L, topk, steps, page):
+    """seq_len + num_steps (or a branch's start + j) beyond the table width: out-of-range draft slots are masked, as in
+    the reference's kernel (eagle_utils.py:889-905 loads with `mask=`), never folded onto the last column."""
+    width = 32
+    r2t = (torch.arange(3 * width, dtype=torch.int32).reshape(3, width) + 1000)
+    rpi = torch.tensor([2, 0])
+    sl = torch.tensor([L, 5])
+    start = draft_token_start(sl, topk, steps, page)
+    want = r2t[rpi].repeat_interleave(topk, 0).clone()
+    for b in range(2):
+        for t in range(topk):
+            for j in range(steps):
+                s, d = int(start[b, t]) + j, int(sl[b]) + j
+                if s < width and d < width:
+                    want[b * topk + t, d] = r2t[rpi[b], s]
+    for _ in range(3):  # same answer every time: no dependence on which duplicate scatter_ keeps
+        assert torch.equal(build_branch_table(r2t, rpi, sl, topk, steps, page), want)
+    buf = torch.zeros((2 * topk, width), dtype=torch.int32)
+    assert torch.equal(build_branch_table(r2t, rpi, sl, topk, steps, page, out=buf), want)

@@ -2,6 +2,8 @@
 tail, in-place LSE merge, duplicate KV-write slots."""
 from __future__ import annotations
 
+import types
+
 import pytest
 import torch
 
@@ -131,3 +133,58 @@ def test_cuda_graph_padding_only_duplicates_the_dummy_slot(device):
     sl[:4] = case.seq_lens.to(device)
     assert ops.check_loc(loc, case.page_size, case.P) == (0, 0)
     assert int((loc[4:] < case.page_size).all())
+
+
+def test_idle_batch_with_a_spec_info_launches_nothing(device):
+    """EAGLE with DP attention hands idle ranks an IDLE / bs == 0 batch that still carries an (idle) EagleDraftInput or
+    EagleVerifyInput.  The reference reads spec_info.kv_indptr and launches nothing; so must this backend, in the eager
+    path and in both CUDA-graph hooks, instead of asking for draft-step rows that an idle input does not have."""
+    case = synth.make_case(2, 8, 2, 128, [40, 50], seed=21)
+    r = H.Runner(case, device)
+    itf = r.itf
+    empty = torch.zeros(0, dtype=torch.int64, device=device)
+    for mode, bs in ((itf.ForwardMode.IDLE, 0), (itf.ForwardMode.DECODE, 0), (itf.ForwardMode.IDLE, 2)):
+        fb = r.batch(itf.ForwardMode.DECODE)
+        fb.forward_mode, fb.batch_size = mode, bs
+        if bs == 0:
+            fb.req_pool_indices, fb.seq_lens = empty, empty
+        fb.spec_info = types.SimpleNamespace()  # no b200_draft_step: an idle input
+        r.backend.init_forward_metadata(fb)
+        md = r.backend.forward_metadata
+        assert md.is_decode and md.bs == 0
+        r.backend.init_forward_metadata_capture_cuda_graph(bs, bs, fb.req_pool_indices, fb.seq_lens, None, mode,
+                                                           fb.spec_info)
+        assert r.backend.forward_metadata.bs == 0
+        r.backend.init_forward_metadata_replay_cuda_graph(bs, fb.req_pool_indices, fb.seq_lens, 0, None, mode,
+                                                          fb.spec_info, None)
+    # a non-empty decode batch with a spec_info but no draft-step rows is still an error
+    fb = r.batch(itf.ForwardMode.DECODE)
+    fb.spec_info = types.SimpleNamespace()
+    with pytest.raises(B200AttnError, match="draft-step rows"):
+        r.backend.init_forward_metadata(fb)
+
+
+def test_fused_write_marker_is_tied_to_the_batch_object_not_its_id(device):
+    """The marker of rotary.forward_fused_kv must not be satisfiable by a LATER batch that CPython gave the id of a
+    collected one: it is stamped on the batch object itself."""
+    case = synth.make_case(2, 8, 2, 128, [300, 200], extend_lens=[100, 200], seed=13)
+    r = H.Runner(case, device)
+    q = case.q.reshape(case.T, -1).to(device)
+    k = case.k_new.reshape(case.T, -1).to(device)
+    v = case.v_new.reshape(case.T, -1).to(device)
+    fb = r.batch()
+    r.backend.init_forward_metadata(fb)
+    r.backend.note_kv_written(r.layer, fb)
+    r.layer.forward(q, k, v, fb, save_kv_cache=False)
+    # a stand-in for "same id, different object": copy the stamp-free attributes into a new batch
+    fb2 = r.batch()
+    assert getattr(fb2, "b200_kv_written", None) is None
+    r.backend.init_forward_metadata(fb2)
+    with pytest.raises(B200AttnError, match="save_kv_cache=False"):
+        r.layer.forward(q, k, v, fb2, save_kv_cache=False)
+    # a stale stamp (an earlier write, another layer's sequence number) does not pass either
+    r.backend.note_kv_written(r.layer, fb2)
+    r.backend.note_kv_written(r.layer, fb)
+    with pytest.raises(B200AttnError, match="save_kv_cache=False"):
+        r.layer.forward(q, k, v, fb2, save_kv_cache=False)
+    r.layer.forward(q, k, v, fb, save_kv_cache=False)

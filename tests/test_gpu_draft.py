@@ -8,6 +8,7 @@ import types
 import pytest
 import torch
 
+import golden_util as gu
 import helpers as H
 from sglang_custom_b200 import interfaces as itf
 from sglang_custom_b200 import synth
@@ -43,6 +44,21 @@ def test_draft_extend_is_causal_extend_over_the_accepted_tokens(kw, device):
     r.backend.speculative_num_steps = None
     out2 = r.forward(fb=_draft_extend_batch(r, accept))
     assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("name", [n for n in gu.DRAFT_EXTEND_FIXTURES if "f32" not in n])
+def test_draft_extend_matches_the_reference_causal_result_not_the_triton_one(name, device):
+    """Outputs of the unmodified reference kernel for the same DRAFT_EXTEND batch, both ways
+    (tests/golden/make_golden_draft_extend.py): the backend reproduces the FlashInfer-style causal result and is
+    measurably away from the Triton backend's (which counts the accepted tokens twice) -- DESIGN.md 3.10."""
+    fx = gu.load(name)
+    r = H.Runner(fx, device)
+    out = r.forward(fb=_draft_extend_batch(r, fx.accept_length.tolist()))
+    dk, dv = r.pools()
+    assert H.pools_equal(dk, fx.ref_k_pool_after) and H.pools_equal(dv, fx.ref_v_pool_after)
+    H.assert_close(out, fx.ref_out_causal, what=f"{name}: vs reference causal (FlashInfer semantics)")
+    gap = (out.float().cpu() - fx.ref_out_triton.float()).abs().max()
+    assert float(gap) > 5 * H.MAX_ABS_TOL, f"{name}: unexpectedly equal to the Triton backend's double-counted result"
 
 
 def test_draft_extend_cuda_graph_hooks(device):

@@ -143,3 +143,40 @@ def test_live_triton_interpreter_equals_restatement():
     r = subprocess.run([sys.executable, "-c", _LIVE.format(root=str(ROOT))], capture_output=True, text=True, env=env,
                        timeout=600)
     assert "LIVE_OK" in r.stdout, r.stderr[-2000:]
+
+
+def _triton_draft_extend(fx):
+    """What the reference's TRITON backend computes for a DRAFT_EXTEND batch (triton_backend.py:265-281): all
+    seq_lens[i] cached slots -- the accepted tokens included -- as an unmasked prefix, then the accepted tokens once
+    more under the causal mask.  Restated in fp32 so the committed reference output can be recognised."""
+    out = torch.zeros_like(fx.q)
+    G = fx.q.shape[1] // fx.ref_k_pool_after.shape[1]
+    start = 0
+    for i in range(fx.seq_lens.numel()):
+        L, E = int(fx.seq_lens[i]), int(fx.accept_length[i])
+        idx = fx.req_to_token[int(fx.req_pool_indices[i]), :L].long()
+        K = torch.cat([fx.ref_k_pool_after[idx], fx.k_new[start:start + E]]).float()
+        V = torch.cat([fx.ref_v_pool_after[idx], fx.v_new[start:start + E]]).float()
+        vis = torch.cat([torch.ones(E, L, dtype=torch.bool), torch.ones(E, E, dtype=torch.bool).tril()], dim=1)
+        for h in range(fx.q.shape[1]):
+            s = (fx.q[start:start + E, h].float() @ K[:, h // G].T * fx.sm_scale).masked_fill(~vis, float("-inf"))
+            out[start:start + E, h] = (torch.softmax(s, -1) @ V[:, h // G]).to(fx.q.dtype)
+        start += E
+    return out
+
+
+@pytest.mark.parametrize("name", gu.DRAFT_EXTEND_FIXTURES)
+def test_draft_extend_deviation_is_pinned_against_both_reference_backends(name):
+    """DRAFT_EXTEND: the reference's two backends disagree (tests/golden/make_golden_draft_extend.py).  The oracle the
+    CUDA path is held to (torch_native extend with prefix = seq_lens - accept_length) is the FlashInfer-style causal
+    result; the Triton-style result counts the accepted tokens twice and is a different number.  Both are outputs of
+    the unmodified reference kernel; this test keeps the difference on record."""
+    fx = gu.load(name)
+    mx, mean = _tol(fx.dtype)
+    prefix = fx.seq_lens - fx.accept_length
+    causal = tn.extend(fx.q, fx.ref_k_pool_after, fx.ref_v_pool_after, fx.req_to_token, fx.req_pool_indices,
+                       fx.seq_lens, prefix, fx.accept_length, fx.sm_scale)
+    H.assert_close(causal, fx.ref_out_causal, max_abs=mx, mean_abs=mean, what=f"{name}: causal")
+    H.assert_close(_triton_draft_extend(fx), fx.ref_out_triton, max_abs=mx, mean_abs=mean, what=f"{name}: triton")
+    gap = (fx.ref_out_causal.float() - fx.ref_out_triton.float()).abs().max()
+    assert float(gap) > 10 * H.MAX_ABS_TOL / 2, "the two reference results must be distinguishable at the parity bound"
