@@ -633,6 +633,27 @@ def _run_reference(args, rank, world):
             "gpu_launches": 0}
 
 
+def _summary(line: dict) -> dict:
+    """The handful of numbers a reader of the line's TAIL needs (the line is long; tools that keep only its last
+    kilobyte lose `extend` / `c4_tp` otherwise).  Pure re-statement of values already on the line, whole job at N GPUs:
+    c2 / c2_e2e GB/s, c3 extend TFLOP/s (+ sustained), c4 GB/s per GPU, c5 ms per layer, parity flags."""
+    def get(obj, *path):
+        for k in path:
+            if not isinstance(obj, dict) or k not in obj:
+                return None
+            obj = obj[k]
+        return obj
+    parity = [get(line, "parity", "ok"), get(line, "parity_n", "ok"), get(line, "extend", "parity_n", "ok"),
+              get(line, "extend", "parity", "ok"), get(line, "c4_tp", "parity_n", "ok"), get(line, "c4_tp", "parity", "ok"),
+              get(line, "c5_mixed", "parity_n", "ok"), get(line, "c5_mixed", "parity", "ok")]
+    seen = [p for p in parity if p is not None]
+    return {"n_gpus": line.get("n_gpus"), "c2": line.get("value"), "c2_e2e": get(line, "e2e", "value"),
+            "c2_roofline_frac": get(line, "roofline", "frac"), "c3_tflops": get(line, "extend", "value"),
+            "c3_sustained": get(line, "extend", "sustained", "value"), "c4_gbs_per_gpu": get(line, "c4_tp", "gbs_per_gpu"),
+            "c5_ms": get(line, "c5_mixed", "ms_per_layer"), "c5_frac_of_bound": get(line, "c5_mixed", "roofline_ms_per_layer", "frac_of_bound"),
+            "parity_all_ok": bool(seen) and all(seen), "parity_checks": len(seen)}
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -694,6 +715,7 @@ def main() -> None:
             line.update(guarded(_run_aux, dev, peaks))
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = _cpu_baseline()
+        line["summary"] = _summary(line)
         print(json.dumps(line), file=_JSON_OUT, flush=True)
     tp.barrier(world)
     if world > 1:

@@ -62,6 +62,9 @@ def test_library_targets_sm100a_and_uses_blackwell_instructions(lib):
     assert dec.get("LDGSTS", 0) > 0 and dec.get("SYNCS", 0) > 0, "decode: LDGSTS gather + mbarrier hand-off"
     assert dec.get("HMMA", 0) > 0 and dec.get("LDSM", 0) > 0, "decode: GQA-packed mma.sync from ldmatrix"
     assert dec.get("F2FP.E4M3", 0) > 0, "decode: FP8 dequantisation in registers"
+    # paged pools (page_size % 16 == 0): K / V tiles arrive as bulk-tensor (TMA) boxes in both hot kernels
+    assert dec.get("UTMALDG", 0) > 0, "decode: no cp.async.bulk.tensor (UTMALDG) in the paged-tile producers"
+    assert tc.get("UTMALDG", 0) > 0, "extend: no cp.async.bulk.tensor (UTMALDG) in the paged-tile producers"
     for fam in c:
         assert c[fam].get("HGMMA", 0) == 0  # wgmma does not exist on sm_100a
 
