@@ -29,6 +29,7 @@
  *   b200attn_check_loc           mem_cache/memory_pool.py:457-458 (`buf[loc] = x`: which duplicates are legal)
  *   b200attn_flatten_kv_indices  layers/attention/utils.py:5-41 (create_flashinfer_kv_indices_triton)
  *   b200attn_gather_kv           torch_native_backend.py:92-94,155-157 (k_cache[per_req_tokens] page gather)
+ *   b200attn_move_kv             mem_cache/memory_pool.py:460-468,1150-1184 (move_kv_cache, all layers in one launch)
  *
  * Conventions
  *   - All pointers are DEVICE pointers unless the name ends in `_host`.
@@ -383,6 +384,21 @@ int b200attn_flatten_kv_indices(const int32_t* req_to_token, int64_t table_strid
                                 const void* req_pool_indices, const void* lens, const void* kv_start,
                                 int idx_is_i64, const int32_t* kv_indptr, int32_t* kv_indices, int bs,
                                 b200attn_stream_t stream);
+
+/* buf[tgt_loc[i]] = buf[src_loc[i]] for i in [0,n), in EVERY buffer of the pool, one launch.
+ * Replaces MHATokenToKVPool.move_kv_cache / copy_all_layer_kv_cache (mem_cache/memory_pool.py:460-468,1150-1184), which
+ * EAGLE calls after a verify step with page_size > 1 and topk > 1 to pull the accepted tokens' K/V together
+ * (speculative/eagle_utils.py:575-583).
+ *   data_ptrs     [n_buffers] uint64, DEVICE array of buffer base addresses (pool.data_ptrs: all k_buffer then v_buffer)
+ *   data_strides  [n_buffers] int64, DEVICE array of row sizes in BYTES (pool.data_strides)
+ *   max_stride_bytes  host copy of max(data_strides) (sizes the grid; no device read-back)
+ *   tgt_loc, src_loc  [n] int64 or int32 row numbers
+ * In-place rule of the reference: every source row is read as it was BEFORE the call, also when it is another pair's
+ * target.  Duplicate targets are unspecified (as there).  Rows / bases that are not 16-byte multiples take a byte path.
+ * Up to 12 800 rows per call (shared-memory staging); more returns B200ATTN_ERR_UNSUPPORTED. */
+int b200attn_move_kv(const uint64_t* data_ptrs, const int64_t* data_strides, int n_buffers,
+                     int64_t max_stride_bytes, const void* tgt_loc, const void* src_loc, int idx_is_i64, int n,
+                     b200attn_stream_t stream);
 
 /* dst[j, :, :] = pool[indices[j], :, :]  -- the page gather `k_cache[per_req_tokens]`, bit exact.
  *   row_bytes = Hkv * D * sizeof(elem) (multiple of 16), pool_tok_stride_bytes likewise */

@@ -64,6 +64,7 @@ SIGNATURES = {
                                    _i, _i, _i, _i, _i, _i, _i, _f, _f, _f, _i, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "b200attn_check_loc": (_i, [_vp, _i, _i64, _i64, _vp, _vp]),
     "b200attn_flatten_kv_indices": (_i, [_vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
+    "b200attn_move_kv": (_i, [_vp, _vp, _i, _i64, _vp, _vp, _i, _i, _vp]),
     "b200attn_gather_kv": (_i, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200attn_transfer_kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),
 }

@@ -55,9 +55,84 @@ __global__ void __launch_bounds__(256) check_loc_kernel(const int64_t* __restric
   if (dup) atomicAdd(flags, dup);
 }
 
+// In-place row move inside every K / V buffer of the pool: buf[tgt[i]] = buf[src[i]] for all i, all buffers, one launch.
+// Reference: MHATokenToKVPool.move_kv_cache + copy_all_layer_kv_cache (mem_cache/memory_pool.py:460-468,1150-1184;
+// caller speculative/eagle_utils.py:575-583).  That kernel loads a 128-byte column block of ALL source rows and only
+// then stores it ("this copy is an inplace operation", :1170-1171), i.e. every read sees the pool as it was before the
+// call even when a row is both a source and a target.  The same rule is kept here with more parallelism: a CTA owns one
+// column slice of one buffer for all n rows, stages the n source slices in shared memory, and stores after a barrier.
+// Distinct CTAs touch disjoint bytes, so there is no ordering between them to get wrong.
+__global__ void __launch_bounds__(256) move_kv_kernel(const uint64_t* __restrict__ data_ptrs,
+                                                      const int64_t* __restrict__ strides, const void* tgt_loc,
+                                                      const void* src_loc, int is_i64, int n, int col_bytes) {
+  extern __shared__ uint4 stage[];
+  uint8_t* base = reinterpret_cast<uint8_t*>(data_ptrs[blockIdx.y]);
+  const int64_t stride = strides[blockIdx.y];
+  const int64_t col0 = static_cast<int64_t>(blockIdx.x) * col_bytes;
+  if (col0 >= stride) return;
+  const int lanes = col_bytes / 16;
+  const int total = n * lanes;
+  const bool vec = ((reinterpret_cast<uintptr_t>(base) | static_cast<uintptr_t>(stride)) & 15u) == 0;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int64_t off = col0 + (idx % lanes) * 16;
+    if (off >= stride) continue;
+    const uint8_t* p = base + load_index(src_loc, is_i64, idx / lanes) * stride + off;
+    if (vec) {
+      stage[idx] = *reinterpret_cast<const uint4*>(p);
+    } else {
+      uint8_t* s = reinterpret_cast<uint8_t*>(stage + idx);
+      const int m = static_cast<int>(stride - off < 16 ? stride - off : 16);
+      for (int b = 0; b < m; ++b) s[b] = p[b];
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int64_t off = col0 + (idx % lanes) * 16;
+    if (off >= stride) continue;
+    uint8_t* p = base + load_index(tgt_loc, is_i64, idx / lanes) * stride + off;
+    if (vec) {
+      *reinterpret_cast<uint4*>(p) = stage[idx];
+    } else {
+      const uint8_t* s = reinterpret_cast<const uint8_t*>(stage + idx);
+      const int m = static_cast<int>(stride - off < 16 ? stride - off : 16);
+      for (int b = 0; b < m; ++b) p[b] = s[b];
+    }
+  }
+}
+
 }  // namespace b200attn
 
 using namespace b200attn;
+
+extern "C" B2_EXPORT int b200attn_move_kv(const uint64_t* data_ptrs, const int64_t* data_strides, int n_buffers,
+                                          int64_t max_stride_bytes, const void* tgt_loc, const void* src_loc,
+                                          int idx_is_i64, int n, b200attn_stream_t stream) {
+  B2_REQUIRE(n >= 0 && n_buffers >= 0 && max_stride_bytes > 0, B200ATTN_ERR_INVALID,
+             "move_kv: bad sizes n=%d n_buffers=%d max_stride_bytes=%lld", n, n_buffers,
+             static_cast<long long>(max_stride_bytes));
+  if (n == 0 || n_buffers == 0) return B200ATTN_OK;
+  B2_REQUIRE(data_ptrs && data_strides && tgt_loc && src_loc, B200ATTN_ERR_INVALID, "move_kv: null pointer");
+  B2_REQUIRE(n_buffers <= 65535, B200ATTN_ERR_UNSUPPORTED, "move_kv: %d buffers > 65535", n_buffers);
+  // widest column slice whose n staged rows fit the shared memory of a CTA (128 B = four full sectors per row)
+  constexpr int64_t kSmemBudget = 200 * 1024;
+  int col = 128;
+  while (col > 16 && static_cast<int64_t>(n) * col > kSmemBudget) col >>= 1;
+  B2_REQUIRE(static_cast<int64_t>(n) * col <= kSmemBudget, B200ATTN_ERR_UNSUPPORTED,
+             "move_kv: %d rows do not fit one CTA's staging (max %lld); split the call", n,
+             static_cast<long long>(kSmemBudget / 16));
+  const size_t smem = static_cast<size_t>(n) * col;
+  static bool configured = false;
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(move_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(kSmemBudget)));
+    configured = true;
+  }
+  dim3 grid(static_cast<unsigned>((max_stride_bytes + col - 1) / col), n_buffers, 1);
+  move_kv_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(data_ptrs, data_strides, tgt_loc, src_loc,
+                                                                         idx_is_i64, n, col);
+  B2_CUDA(cudaGetLastError());
+  return B200ATTN_OK;
+}
 
 extern "C" B2_EXPORT int b200attn_check_loc(const int64_t* loc, int T, int64_t dummy_rows, int64_t pool_rows,
                                             int32_t* flags, b200attn_stream_t stream) {

@@ -102,6 +102,17 @@ class MHATokenToKVPool:
         shape = (size + page_size, head_num, head_dim)
         self.k_buffer = [torch.zeros(shape, dtype=self.store_dtype, device=device) for _ in range(layer_num)]
         self.v_buffer = [torch.zeros(shape, dtype=self.store_dtype, device=device) for _ in range(layer_num)]
+        # memory_pool.py:256-268: base address and row size (bytes) of every K then every V buffer, on the device
+        bufs = self.k_buffer + self.v_buffer
+        self.token_stride = head_num * head_dim
+        self.data_ptrs = torch.tensor([x.data_ptr() for x in bufs], dtype=torch.uint64, device=device)
+        self._row_bytes = [x[0].numel() * x.element_size() for x in bufs]
+        self.data_strides = torch.tensor(self._row_bytes, dtype=torch.int64, device=device)
+
+    def move_kv_cache(self, tgt_loc: torch.Tensor, src_loc: torch.Tensor) -> None:
+        """memory_pool.py:460-468: all layers, K and V, in one launch (b200attn_move_kv); no torch fallback."""
+        from . import ops
+        ops.move_kv(self.data_ptrs, self.data_strides, max(self._row_bytes), tgt_loc, src_loc)
 
     def _view(self, buf: torch.Tensor) -> torch.Tensor:
         return buf.view(self.dtype) if self.store_dtype != self.dtype else buf

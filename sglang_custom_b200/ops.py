@@ -444,6 +444,24 @@ def flatten_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tenso
         _stream(req_to_token)), "b200attn_flatten_kv_indices")
 
 
+def move_kv(data_ptrs: torch.Tensor, data_strides: torch.Tensor, max_stride_bytes: int, tgt_loc: torch.Tensor,
+            src_loc: torch.Tensor) -> None:
+    """buf[tgt_loc] = buf[src_loc] in every buffer listed in data_ptrs (uint64 addresses) / data_strides (int64 row bytes),
+    one launch -- MHATokenToKVPool.move_kv_cache (memory_pool.py:460-468).  Sources are read as they were before the
+    call (the reference's in-place rule, :1170-1171)."""
+    _cuda(data_ptrs, data_strides, tgt_loc, src_loc)
+    if data_ptrs.dtype not in (torch.uint64, torch.int64) or data_strides.dtype != torch.int64:
+        raise B200AttnError("move_kv: data_ptrs must be uint64 / int64 and data_strides int64")
+    if not (data_ptrs.is_contiguous() and data_strides.is_contiguous() and tgt_loc.is_contiguous()
+            and src_loc.is_contiguous()):
+        raise B200AttnError("move_kv: arguments must be contiguous")
+    if data_ptrs.numel() != data_strides.numel() or tgt_loc.numel() != src_loc.numel() or tgt_loc.dtype != src_loc.dtype:
+        raise B200AttnError("move_kv: data_ptrs / data_strides and tgt_loc / src_loc must pair up")
+    check(_lib.load().b200attn_move_kv(
+        data_ptrs.data_ptr(), data_strides.data_ptr(), data_ptrs.numel(), int(max_stride_bytes), tgt_loc.data_ptr(),
+        src_loc.data_ptr(), _is_i64(tgt_loc), tgt_loc.numel(), _stream(tgt_loc)), "b200attn_move_kv")
+
+
 def gather_kv(pool: torch.Tensor, indices: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[j] = pool[indices[j]] -- the page gather `k_cache[per_req_tokens]`, bit exact."""
     _cuda(pool, indices, out)

@@ -7,6 +7,7 @@ import torch
 from oracle import exact
 from oracle import torch_native as tn
 from sglang_custom_b200 import ops
+from sglang_custom_b200._lib import B200AttnError
 
 pytestmark = pytest.mark.gpu
 
@@ -64,3 +65,44 @@ def test_gather_kv_bit_exact(dtype, Hkv, D, device):
     want = pool[idx.long()]
     assert torch.equal(got.view(torch.uint8), want.view(torch.uint8))
     assert torch.equal(exact.gather_rows(pool, idx).view(torch.uint8), want.view(torch.uint8))
+
+
+@pytest.mark.parametrize("dtype,head_num,head_dim,layers,n", [
+    (torch.bfloat16, 8, 128, 4, 37),          # 2 KiB rows
+    (torch.float8_e4m3fn, 1, 128, 3, 300),    # 128-byte FP8 rows (C4 / C5 at TP 8), stored as uint8
+    (torch.bfloat16, 2, 13, 2, 9),            # 52-byte rows: not a multiple of 16 -> byte path
+    (torch.float16, 4, 64, 2, 5000),          # many rows: narrower column slices per CTA
+])
+def test_move_kv_cache_moves_rows_in_every_layer_like_the_reference(dtype, head_num, head_dim, layers, n, device):
+    """MHATokenToKVPool.move_kv_cache (memory_pool.py:460-468,1150-1184), used by EAGLE after a verify step with
+    page_size > 1 and topk > 1 (eagle_utils.py:575-583): buf[tgt] = buf[src] in all K and V buffers, every source row
+    read as it was before the call -- also rows that are somebody else's target (the reference loads a whole column
+    block of all rows before it stores)."""
+    from sglang_custom_b200 import interfaces as itf
+    size = 8192
+    pool = itf.MHATokenToKVPool(size, 16, dtype, head_num, head_dim, layers, str(device))
+    g = torch.Generator(device=device).manual_seed(n)
+    for buf in pool.k_buffer + pool.v_buffer:
+        buf.copy_(torch.randint(0, 255, buf.shape, generator=g, device=device, dtype=torch.uint8).view(torch.uint8)
+                  if buf.dtype == torch.uint8 else torch.randn(buf.shape, generator=g, device=device).to(buf.dtype))
+    before = [b.clone() for b in pool.k_buffer + pool.v_buffer]
+    perm = torch.randperm(size, generator=g, device=device) + 16
+    tgt = perm[:n].clone()
+    src = perm[n // 2:n // 2 + n].clone()   # overlaps tgt: half of the sources are overwritten by this very call
+    pool.move_kv_cache(tgt, src)
+    torch.cuda.synchronize(device)
+    for got, old in zip(pool.k_buffer + pool.v_buffer, before):
+        want = old.clone()
+        want[tgt] = old[src]
+        assert torch.equal(got.view(torch.uint8), want.view(torch.uint8))
+    # int32 locations, and an empty call
+    pool.move_kv_cache(tgt.to(torch.int32)[:3], src.to(torch.int32)[:3])
+    pool.move_kv_cache(tgt[:0], src[:0])
+
+
+def test_move_kv_rejects_more_rows_than_one_cta_can_stage(device):
+    from sglang_custom_b200 import interfaces as itf
+    pool = itf.MHATokenToKVPool(20000, 1, torch.bfloat16, 1, 64, 1, str(device))
+    loc = torch.arange(13000, device=device)
+    with pytest.raises(B200AttnError, match="UNSUPPORTED"):
+        pool.move_kv_cache(loc, loc)
